@@ -1,0 +1,468 @@
+// Host orchestration of the B200 step engine (see engine.h). All kernels live in this TU.
+#include "engine.h"
+
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <stdexcept>
+
+#include "kernels_obs.cuh"
+#include "kernels_reset.cuh"
+#include "kernels_step.cuh"
+
+namespace gd {
+
+#define GD_CUDA(expr)                                                                         \
+    do {                                                                                      \
+        cudaError_t e__ = (expr);                                                             \
+        if (e__ != cudaSuccess)                                                               \
+            throw std::runtime_error(std::string("CUDA error: ") + cudaGetErrorString(e__) +  \
+                                     " at " #expr);                                           \
+    } while (0)
+
+static constexpr int AGENTS_BLOCK = 256;
+static constexpr size_t ARENA_SLAB = 256ull << 20;
+
+template <typename T>
+static T *devAlloc(std::vector<void *> &owned, size_t count, int fill_byte = 0) {
+    void *p = nullptr;
+    size_t bytes = std::max<size_t>(count * sizeof(T), 16);
+    GD_CUDA(cudaMalloc(&p, bytes));
+    GD_CUDA(cudaMemset(p, fill_byte, bytes));
+    owned.push_back(p);
+    return static_cast<T *>(p);
+}
+
+Engine::Engine(int gpu_id, int max_agents, const Params &params, const std::vector<std::string> &scenes)
+    : gpu_(gpu_id), W_((int)scenes.size()), S_(max_agents), params_(params)
+{
+    if (W_ <= 0) throw std::runtime_error("SimManager needs at least one scene (num_worlds = len(scenes))");
+    if (S_ < 2 || S_ > 128) throw std::runtime_error("max_agents must be in [2, 128]");
+    if (params_.rewardType == RW_Dense)
+        throw std::runtime_error("RewardType.Dense is not implemented by the reference (src/sim.cpp:579-583)");
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0)
+        throw std::runtime_error("gpudrive_b200: no CUDA device visible; this engine has no CPU fallback");
+    if (gpu_ < 0 || gpu_ >= ndev) throw std::runtime_error("gpu_id out of range");
+    GD_CUDA(cudaSetDevice(gpu_));
+    GD_CUDA(cudaStreamCreateWithFlags(&stream_, cudaStreamNonBlocking));
+
+    allocExports();
+
+    scene_paths_ = scenes;
+    deleted_.assign(W_, {});
+    world_scene_.assign(W_, 0);
+    for (int w = 0; w < W_; w++) world_scene_[w] = sceneFor(scenes[w], deleted_[w]);
+    GD_CUDA(cudaMemcpy(st_.world_scene, world_scene_.data(), W_ * sizeof(int32_t), cudaMemcpyHostToDevice));
+
+    GD_CUDA(cudaFuncSetAttribute(k_obs, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(ObsSmem)));
+
+    // Sim::Sim -> createPersistentEntities + initWorld for every world, then Manager's ctor reset({})
+    std::vector<int32_t> all(W_);
+    for (int w = 0; w < W_; w++) all[w] = w;
+    launchBindReset(all, true);
+    launchRest(false);
+    sync();
+}
+
+Engine::~Engine() {
+    cudaSetDevice(gpu_);
+    cudaDeviceSynchronize();
+    for (void *p : owned_) cudaFree(p);
+    for (void *p : arena_slabs_) cudaFree(p);
+    if (d_scenes_) cudaFree(d_scenes_);
+    if (h_pinned_actions_) cudaFreeHost(h_pinned_actions_);
+    if (stream_) cudaStreamDestroy(stream_);
+}
+
+void Engine::allocExports() {
+    const size_t WS = (size_t)W_ * S_;
+    ex_.action = devAlloc<float>(owned_, WS * kActionSize);
+    ex_.reward = devAlloc<float>(owned_, WS);
+    ex_.done = devAlloc<int32_t>(owned_, WS);
+    ex_.info = devAlloc<int32_t>(owned_, WS * kInfoSize);
+    ex_.self_obs = devAlloc<float>(owned_, WS * kSelfObsSize);
+    ex_.abs_obs = devAlloc<float>(owned_, WS * kAbsObsSize);
+    ex_.partner_obs = devAlloc<float>(owned_, WS * (S_ - 1) * kPartnerObsSize);
+    ex_.agent_roadmap = devAlloc<float>(owned_, WS * kMaxAgentMapObs * kMapObsSize);
+    ex_.map_obs = devAlloc<float>(owned_, (size_t)W_ * kMaxRoadEntityCount * kMapObsSize);
+    ex_.lidar = devAlloc<float>(owned_, WS * 3 * kNumLidarSamples * kLidarRowSize);
+    ex_.steps_remaining = devAlloc<int32_t>(owned_, WS);
+    ex_.shape = devAlloc<int32_t>(owned_, (size_t)W_ * 2);
+    ex_.controlled = devAlloc<int32_t>(owned_, WS);
+    ex_.response = devAlloc<int32_t>(owned_, WS);
+    ex_.traj = devAlloc<float>(owned_, WS * kTrajSize);
+    ex_.world_means = devAlloc<float>(owned_, (size_t)W_ * 3);
+    ex_.metadata = devAlloc<int32_t>(owned_, WS * kMetaSize);
+    ex_.deleted = devAlloc<int32_t>(owned_, WS, 0xff);    // Sim::Sim fills -1 (src/sim.cpp:1003-1006)
+    ex_.map_name = devAlloc<int32_t>(owned_, (size_t)W_ * 32);
+    ex_.scenario_id = devAlloc<int32_t>(owned_, (size_t)W_ * 32);
+    ex_.valid_state = devAlloc<int32_t>(owned_, WS);
+    ex_.knn_idx = devAlloc<int32_t>(owned_, WS * kMaxAgentMapObs, 0xff);
+    st_.pos = devAlloc<float4>(owned_, WS);
+    st_.rv = devAlloc<float4>(owned_, WS);
+    st_.collided = devAlloc<int32_t>(owned_, WS);
+    st_.world_scene = devAlloc<int32_t>(owned_, W_);
+    st_.reset_flag = devAlloc<int32_t>(owned_, W_);
+    st_.stats = devAlloc<unsigned long long>(owned_, 16);
+    d_worklist_ = devAlloc<int32_t>(owned_, W_);
+}
+
+void *Engine::arenaAlloc(size_t bytes) {
+    bytes = (bytes + 255) & ~size_t(255);
+    if (arena_slabs_.empty() || arena_off_ + bytes > arena_cap_) {
+        size_t cap = std::max(ARENA_SLAB, bytes);
+        void *p = nullptr;
+        GD_CUDA(cudaMalloc(&p, cap));
+        arena_slabs_.push_back(p);
+        arena_off_ = 0;
+        arena_cap_ = cap;
+    }
+    void *out = static_cast<char *>(arena_slabs_.back()) + arena_off_;
+    arena_off_ += bytes;
+    return out;
+}
+
+// Pack one SceneData into a contiguous blob, upload it into the pool arena, register its SceneDev.
+int Engine::uploadScene(const SceneData &s, const std::string &key) {
+    const int R = s.numRoads, A = s.numAgents;
+    const int Rpad = (R + 31) & ~31;
+    // collidable subset: road edges + stop signs (everything else is in Sim::collisionPairs' ignore list
+    // for every agent type, src/sim.hpp:88-102)
+    std::vector<int> coll;
+    for (int r = 0; r < R; r++)
+        if (s.rtype[r] == ET_RoadEdge || s.rtype[r] == ET_StopSign) coll.push_back(r);
+    const int C = (int)coll.size(), Cpad = (C + 31) & ~31;
+
+    SceneDev dev;
+    memset(&dev, 0, sizeof(dev));
+    // z classes
+    std::vector<uint8_t> zcls(R, 0);
+    for (int r = 0; r < R; r++) {
+        int c = -1;
+        for (int k = 0; k < dev.numZClasses; k++)
+            if (dev.zc_z[k] == s.rz[r] && dev.zc_d2[k] == s.rd2[r]) { c = k; break; }
+        if (c < 0) {
+            if (dev.numZClasses >= kMaxZClasses) throw std::runtime_error("too many distinct road z-classes");
+            c = dev.numZClasses++;
+            dev.zc_z[c] = s.rz[r];
+            dev.zc_d2[c] = s.rd2[r];
+        }
+        zcls[r] = (uint8_t)c;
+    }
+
+    size_t off = 0;
+    auto section = [&](size_t bytes) { size_t o = off; off += (bytes + 15) & ~size_t(15); return o; };
+    const size_t o_ra = section(sizeof(float4) * Rpad), o_rb = section(sizeof(float2) * Rpad),
+                 o_rc = section(sizeof(uint32_t) * Rpad), o_rd = section(sizeof(float4) * Rpad),
+                 o_cc = section(sizeof(float4) * Cpad), o_co = section(sizeof(float4) * 4 * Cpad),
+                 o_tr = section(sizeof(float) * (size_t)A * kTrajSize), o_aa = section(sizeof(float4) * A),
+                 o_ab = section(sizeof(float4) * A), o_ac = section(sizeof(float4) * A),
+                 o_me = section(sizeof(int4) * A);
+    std::vector<unsigned char> blob(off, 0);
+    auto F4 = [&](size_t o) { return reinterpret_cast<float4 *>(blob.data() + o); };
+    float4 *ra = F4(o_ra), *rd = F4(o_rd), *cc = F4(o_cc), *co = F4(o_co), *aa = F4(o_aa), *ab = F4(o_ab), *ac = F4(o_ac);
+    float2 *rb = reinterpret_cast<float2 *>(blob.data() + o_rb);
+    uint32_t *rc = reinterpret_cast<uint32_t *>(blob.data() + o_rc);
+    int4 *me = reinterpret_cast<int4 *>(blob.data() + o_me);
+    for (int r = 0; r < R; r++) {
+        ra[r] = make_float4(s.rx[r], s.ry[r], s.rqw[r], s.rqz[r]);
+        rb[r] = make_float2(s.rd0[r], s.rd1[r]);
+        rc[r] = (uint32_t)zcls[r] | ((uint32_t)s.rtype[r] << 8);
+        rd[r] = make_float4(s.rd2[r], s.ryaw[r], s.rid[r], (float)s.rmaptype[r]);
+    }
+    for (int r = R; r < Rpad; r++) {   // padding far away, never in any radius
+        ra[r] = make_float4(1e30f, 1e30f, 1.f, 0.f);
+        rb[r] = make_float2(1.f, 1.f);
+    }
+    for (int i = 0; i < C; i++) {
+        const int r = coll[i];
+        // OrientedBoundingBox2D::from on the host: same libm calls as the reference's CPU build
+        const float theta = s.ryaw[r];
+        const float cth = cosf(theta), sth = sinf(theta);
+        const float Xx = cth * s.rd0[r], Xy = sth * s.rd0[r];
+        const float Yx = -sth * s.rd1[r], Yy = cth * s.rd1[r];
+        const float px = s.rx[r], py = s.ry[r];
+        float cx[4], cy[4];
+        cx[0] = (px - Xx) - Yx; cy[0] = (py - Xy) - Yy;
+        cx[1] = (px + Xx) - Yx; cy[1] = (py + Xy) - Yy;
+        cx[2] = (px + Xx) + Yx; cy[2] = (py + Xy) + Yy;
+        cx[3] = (px - Xx) + Yx; cy[3] = (py - Xy) + Yy;
+        float a0x = cx[1] - cx[0], a0y = cy[1] - cy[0], a1x = cx[3] - cx[0], a1y = cy[3] - cy[0];
+        float inv0 = 1.f / (a0x * a0x + a0y * a0y), inv1 = 1.f / (a1x * a1x + a1y * a1y);
+        a0x *= inv0; a0y *= inv0; a1x *= inv1; a1y *= inv1;
+        const float org0 = cx[0] * a0x + cy[0] * a0y, org1 = cx[0] * a1x + cy[0] * a1y;
+        co[i * 4 + 0] = make_float4(cx[0], cy[0], cx[1], cy[1]);
+        co[i * 4 + 1] = make_float4(cx[2], cy[2], cx[3], cy[3]);
+        co[i * 4 + 2] = make_float4(a0x, a0y, a1x, a1y);
+        co[i * 4 + 3] = make_float4(org0, org1, s.rz[r], s.rd2[r]);
+        const float rad = sqrtf(s.rd0[r] * s.rd0[r] + s.rd1[r] * s.rd1[r]) * 1.0001f + 1e-3f;
+        cc[i] = make_float4(px, py, rad, (float)s.rtype[r]);
+    }
+    for (int i = C; i < Cpad; i++) cc[i] = make_float4(1e30f, 1e30f, 0.f, 0.f);
+    if (A) memcpy(blob.data() + o_tr, s.traj.data(), sizeof(float) * (size_t)A * kTrajSize);
+    for (int a = 0; a < A; a++) {
+        aa[a] = make_float4(s.vsize[a * 3], s.vsize[a * 3 + 1], s.vsize[a * 3 + 2], (float)s.id[a]);
+        ab[a] = make_float4(s.scale[a * 3], s.scale[a * 3 + 1], s.scale[a * 3 + 2], (float)s.type[a]);
+        ac[a] = make_float4(s.goal[a * 2], s.goal[a * 2 + 1], (float)s.response[a], (float)s.controlled[a]);
+        me[a] = make_int4(s.meta[a * 4], s.meta[a * 4 + 1], s.meta[a * 4 + 2], s.meta[a * 4 + 3]);
+    }
+    char *base = static_cast<char *>(arenaAlloc(blob.size()));
+    GD_CUDA(cudaMemcpy(base, blob.data(), blob.size(), cudaMemcpyHostToDevice));
+    dev.road_a = reinterpret_cast<const float4 *>(base + o_ra);
+    dev.road_b = reinterpret_cast<const float2 *>(base + o_rb);
+    dev.road_c = reinterpret_cast<const uint32_t *>(base + o_rc);
+    dev.road_d = reinterpret_cast<const float4 *>(base + o_rd);
+    dev.coll_cull = reinterpret_cast<const float4 *>(base + o_cc);
+    dev.coll_obb = reinterpret_cast<const float4 *>(base + o_co);
+    dev.traj = reinterpret_cast<const float *>(base + o_tr);
+    dev.ag_a = reinterpret_cast<const float4 *>(base + o_aa);
+    dev.ag_b = reinterpret_cast<const float4 *>(base + o_ab);
+    dev.ag_c = reinterpret_cast<const float4 *>(base + o_ac);
+    dev.meta = reinterpret_cast<const int4 *>(base + o_me);
+    dev.numRoads = R; dev.numAgents = A; dev.numColl = C;
+    dev.mean[0] = s.mean[0]; dev.mean[1] = s.mean[1]; dev.mean[2] = s.mean[2];
+    memcpy(dev.mapName, s.mapName, sizeof(dev.mapName));
+    memcpy(dev.scenarioId, s.scenarioId, sizeof(dev.scenarioId));
+
+    SceneHost h;
+    h.key = key; h.dev = dev; h.numAgents = A; h.numRoads = R; h.numControlled = s.numControlled;
+    scenes_.push_back(h);
+    scene_index_[key] = (int)scenes_.size() - 1;
+    max_roads_ = std::max(max_roads_, R);
+    scene_table_dirty_ = true;
+    return (int)scenes_.size() - 1;
+}
+
+int Engine::sceneFor(const std::string &path, const std::vector<int32_t> &deleted) {
+    std::string key = path;
+    if (!deleted.empty()) {
+        key += "#del";
+        for (int32_t d : deleted) key += ":" + std::to_string(d);
+    }
+    auto it = scene_index_.find(key);
+    if (it != scene_index_.end()) return it->second;
+    std::shared_ptr<ParsedMap> pm;
+    auto pit = parsed_cache_.find(path);
+    if (pit != parsed_cache_.end()) pm = pit->second;
+    else {
+        pm = std::make_shared<ParsedMap>(parseMapFile(path, params_.polylineReductionThreshold));
+        if (parsed_cache_.size() < 64) parsed_cache_[path] = pm;   // small LRU-less cache for deleteAgents
+    }
+    SceneData s = buildScene(*pm, params_, S_, deleted.data(), (int)deleted.size());
+    return uploadScene(s, key);
+}
+
+void Engine::syncSceneTable() {
+    if (!scene_table_dirty_) return;
+    if (scenes_.size() > d_scenes_cap_) {
+        GD_CUDA(cudaStreamSynchronize(stream_));
+        if (d_scenes_) GD_CUDA(cudaFree(d_scenes_));
+        d_scenes_cap_ = std::max<size_t>(scenes_.size() * 2, 64);
+        GD_CUDA(cudaMalloc(&d_scenes_, d_scenes_cap_ * sizeof(SceneDev)));
+    }
+    std::vector<SceneDev> tmp(scenes_.size());
+    for (size_t i = 0; i < scenes_.size(); i++) tmp[i] = scenes_[i].dev;
+    GD_CUDA(cudaMemcpy(d_scenes_, tmp.data(), tmp.size() * sizeof(SceneDev), cudaMemcpyHostToDevice));
+    scene_table_dirty_ = false;
+}
+
+void Engine::launchBindReset(const std::vector<int32_t> &worlds, bool rebind) {
+    if (worlds.empty()) return;
+    syncSceneTable();
+    const int n = (int)worlds.size();
+    GD_CUDA(cudaMemcpyAsync(d_worklist_, worlds.data(), n * sizeof(int32_t), cudaMemcpyHostToDevice, stream_));
+    if (rebind) {
+        k_bind<<<dim3(n, BIND_SPLIT), 256, 0, stream_>>>(d_worklist_, d_scenes_, st_, ex_, S_);
+        launches_++;
+    }
+    const int blk = ((S_ + 31) / 32) * 32;
+    k_reset<<<n, blk, 0, stream_>>>(d_worklist_, d_scenes_, st_, ex_, S_, params_.dynamicsModel);
+    launches_++;
+    GD_CUDA(cudaGetLastError());
+    // the pageable worklist buffer must stay alive until the copy is consumed
+    GD_CUDA(cudaStreamSynchronize(stream_));
+    episodes_reset_ += n;
+}
+
+// setupRestOfTasks (src/sim.cpp:785-943): collisions, reward, (--t), done, observation fan-out
+void Engine::launchRest(bool decrement) {
+    syncSceneTable();
+    const size_t smem_agents = sizeof(AgentBox) * (size_t)S_;
+    k_agents<AGENTS_BLOCK><<<W_, AGENTS_BLOCK, smem_agents, stream_>>>(d_scenes_, st_, ex_, params_, S_,
+                                                                    decrement ? 1 : 0, decrement ? 1 : 0);
+    const int groups = (S_ + OBS_WARPS - 1) / OBS_WARPS;
+    k_obs<<<W_ * groups, OBS_BLOCK, sizeof(ObsSmem), stream_>>>(d_scenes_, st_, ex_, params_, S_, groups, 1);
+    launches_ += 2;
+    kernels_per_step_ = 2;
+    GD_CUDA(cudaGetLastError());
+}
+
+void Engine::stepAsync() {
+    GD_CUDA(cudaSetDevice(gpu_));
+    launchRest(true);
+    steps_++;
+}
+
+void Engine::sync() { GD_CUDA(cudaStreamSynchronize(stream_)); }
+
+void Engine::step() {
+    stepAsync();
+    sync();
+}
+
+void Engine::reset(const int32_t *worlds, int n) {
+    GD_CUDA(cudaSetDevice(gpu_));
+    // python may have written tensors on another stream; reference semantics are fully synchronous
+    GD_CUDA(cudaDeviceSynchronize());
+    std::vector<int32_t> list;
+    for (int i = 0; i < n; i++) {
+        if (worlds[i] < 0 || worlds[i] >= W_) throw std::runtime_error("reset: world index out of range");
+        list.push_back(worlds[i]);
+    }
+    std::sort(list.begin(), list.end());
+    list.erase(std::unique(list.begin(), list.end()), list.end());
+    launchBindReset(list, false);
+    launchRest(false);     // the Reset graph recomputes every world (src/sim.cpp:960-966)
+    sync();
+}
+
+void Engine::setMaps(const std::vector<std::string> &scenes) {
+    if ((int)scenes.size() != W_) throw std::runtime_error("set_maps: len(maps) must equal num_worlds");
+    GD_CUDA(cudaSetDevice(gpu_));
+    GD_CUDA(cudaDeviceSynchronize());
+    scene_paths_ = scenes;
+    for (int w = 0; w < W_; w++) {
+        deleted_[w].clear();                         // src/mgr.cpp:643-646
+        world_scene_[w] = sceneFor(scenes[w], deleted_[w]);
+    }
+    GD_CUDA(cudaMemset(ex_.deleted, 0xff, (size_t)W_ * S_ * sizeof(int32_t)));
+    GD_CUDA(cudaMemcpy(st_.world_scene, world_scene_.data(), W_ * sizeof(int32_t), cudaMemcpyHostToDevice));
+    std::vector<int32_t> all(W_);
+    for (int w = 0; w < W_; w++) all[w] = w;
+    launchBindReset(all, true);
+    launchRest(false);
+    sync();
+}
+
+void Engine::deleteAgents(int world, const int32_t *ids, int n) {
+    if (world < 0 || world >= W_) throw std::runtime_error("deleteAgents: world index out of range");
+    if (n > S_) throw std::runtime_error("deleteAgents: more ids than agent slots");
+    GD_CUDA(cudaSetDevice(gpu_));
+    GD_CUDA(cudaDeviceSynchronize());
+    // src/mgr.cpp:698-709: ids overwrite the head of the world's DeletedAgents list
+    std::vector<int32_t> cur(S_);
+    GD_CUDA(cudaMemcpy(cur.data(), ex_.deleted + (size_t)world * S_, S_ * sizeof(int32_t), cudaMemcpyDeviceToHost));
+    for (int i = 0; i < n; i++) cur[i] = ids[i];
+    GD_CUDA(cudaMemcpy(ex_.deleted + (size_t)world * S_, cur.data(), S_ * sizeof(int32_t), cudaMemcpyHostToDevice));
+    deleted_[world].clear();
+    for (int i = 0; i < S_; i++)
+        if (cur[i] != -1) deleted_[world].push_back(cur[i]);
+    world_scene_[world] = sceneFor(scene_paths_[world], deleted_[world]);
+    GD_CUDA(cudaMemcpy(st_.world_scene + world, &world_scene_[world], sizeof(int32_t), cudaMemcpyHostToDevice));
+    // the reference then resets every world; only `world` has ResetMap set (src/mgr.cpp:707-714)
+    launchBindReset({world}, true);
+    std::vector<int32_t> others;
+    for (int w = 0; w < W_; w++)
+        if (w != world) others.push_back(w);
+    launchBindReset(others, false);
+    launchRest(false);
+    sync();
+}
+
+int Engine::poolAdd(const std::string &path) {
+    GD_CUDA(cudaSetDevice(gpu_));
+    return sceneFor(path, {});
+}
+
+void Engine::bindWorlds(const int32_t *worlds, const int32_t *scene_ids, int n) {
+    GD_CUDA(cudaSetDevice(gpu_));
+    GD_CUDA(cudaDeviceSynchronize());
+    std::vector<int32_t> list;
+    for (int i = 0; i < n; i++) {
+        if (worlds[i] < 0 || worlds[i] >= W_) throw std::runtime_error("bind: world index out of range");
+        if (scene_ids[i] < 0 || scene_ids[i] >= (int)scenes_.size()) throw std::runtime_error("bind: scene id out of range");
+        world_scene_[worlds[i]] = scene_ids[i];
+        scene_paths_[worlds[i]] = scenes_[scene_ids[i]].key;
+        list.push_back(worlds[i]);
+    }
+    GD_CUDA(cudaMemcpy(st_.world_scene, world_scene_.data(), W_ * sizeof(int32_t), cudaMemcpyHostToDevice));
+    launchBindReset(list, true);
+    launchRest(false);
+    sync();
+}
+
+void Engine::stepHost(const float *actions, int action_cols, float *reward, int32_t *done, int32_t *info) {
+    GD_CUDA(cudaSetDevice(gpu_));
+    const size_t WS = (size_t)W_ * S_;
+    if (action_cols <= 0 || action_cols > kActionSize) throw std::runtime_error("stepHost: action_cols must be in [1, 10]");
+    if (actions) {
+        GD_CUDA(cudaMemcpy2DAsync(ex_.action, kActionSize * sizeof(float), actions, action_cols * sizeof(float),
+                                  action_cols * sizeof(float), WS, cudaMemcpyHostToDevice, stream_));
+    }
+    stepAsync();
+    if (reward) GD_CUDA(cudaMemcpyAsync(reward, ex_.reward, WS * sizeof(float), cudaMemcpyDeviceToHost, stream_));
+    if (done) GD_CUDA(cudaMemcpyAsync(done, ex_.done, WS * sizeof(int32_t), cudaMemcpyDeviceToHost, stream_));
+    if (info) GD_CUDA(cudaMemcpyAsync(info, ex_.info, WS * kInfoSize * sizeof(int32_t), cudaMemcpyDeviceToHost, stream_));
+    sync();
+}
+
+StepStats Engine::stats() {
+    StepStats s;
+    memset(&s, 0, sizeof(s));
+    s.steps = steps_;
+    s.episodes_reset = episodes_reset_;
+    uint64_t live = 0, ctrl = 0;
+    for (int w = 0; w < W_; w++) {
+        live += scenes_[world_scene_[w]].numAgents;
+        ctrl += scenes_[world_scene_[w]].numControlled;
+    }
+    s.agent_steps = live * steps_;          // exact while the world->scene binding is unchanged
+    s.controlled_steps = ctrl * steps_;
+    return s;
+}
+
+TensorDesc Engine::tensor(int id) const {
+    TensorDesc d;
+    memset(&d, 0, sizeof(d));
+    d.device = gpu_;
+    auto set = [&](void *p, int dtype, std::initializer_list<int64_t> shp) {
+        d.ptr = p; d.dtype = dtype; d.ndim = (int)shp.size();
+        int i = 0;
+        for (int64_t v : shp) d.shape[i++] = v;
+    };
+    const int64_t W = W_, S = S_;
+    switch (id) {
+    case T_ACTION: set(ex_.action, 0, {W, S, kActionSize}); break;
+    case T_REWARD: set(ex_.reward, 0, {W, S, 1}); break;
+    case T_DONE: set(ex_.done, 1, {W, S, 1}); break;
+    case T_SELF_OBS: set(ex_.self_obs, 0, {W, S, kSelfObsSize}); break;
+    case T_MAP_OBS: set(ex_.map_obs, 0, {W, kMaxRoadEntityCount, kMapObsSize}); break;
+    case T_PARTNER_OBS: set(ex_.partner_obs, 0, {W, S, S - 1, kPartnerObsSize}); break;
+    case T_AGENT_ROADMAP: set(ex_.agent_roadmap, 0, {W, S, kMaxAgentMapObs, kMapObsSize}); break;
+    case T_LIDAR: set(ex_.lidar, 0, {W, S, 3, kNumLidarSamples, kLidarRowSize}); break;
+    case T_STEPS_REMAINING: set(ex_.steps_remaining, 1, {W, S, 1}); break;
+    case T_SHAPE: set(ex_.shape, 1, {W, 2}); break;
+    case T_CONTROLLED: set(ex_.controlled, 1, {W, S, 1}); break;
+    case T_ABS_OBS: set(ex_.abs_obs, 0, {W, S, kAbsObsSize}); break;
+    case T_VALID_STATE: set(ex_.valid_state, 1, {W, S, 1}); break;
+    case T_INFO: set(ex_.info, 1, {W, S, kInfoSize}); break;
+    case T_RESPONSE: set(ex_.response, 1, {W, S, 1}); break;
+    case T_TRAJ: set(ex_.traj, 0, {W, S, kTrajSize}); break;
+    case T_WORLD_MEANS: set(ex_.world_means, 0, {W, 3}); break;
+    case T_METADATA: set(ex_.metadata, 1, {W, S, kMetaSize}); break;
+    case T_DELETED: set(ex_.deleted, 1, {W, S}); break;
+    case T_MAP_NAME: set(ex_.map_name, 1, {W, 32}); break;
+    case T_SCENARIO_ID: set(ex_.scenario_id, 1, {W, 32}); break;
+    case T_KNN_IDX: set(ex_.knn_idx, 1, {W, S, kMaxAgentMapObs}); break;
+    case T_BEV:
+        throw std::runtime_error("bev_observation_tensor: BEV rasterisation is not built in this engine yet "
+                                 "(160 KB per agent slot; optional row 8(f)-2)");
+    default: throw std::runtime_error("unknown tensor id");
+    }
+    return d;
+}
+
+} // namespace gd

@@ -1,0 +1,163 @@
+// Host manager of the B200 step engine: owns the device scenario pool, the world state and the
+// export buffers, and launches the step / reset kernels. Replaces Manager::Impl + the Madrona
+// executors behind src/mgr.cpp:399-588 for ExecMode::CUDA.
+#pragma once
+#include <cstdint>
+#include <map>
+#include <memory>
+#include <string>
+#include <vector>
+
+#include <cuda_runtime.h>
+
+#include "gd_types.h"
+#include "scenario.h"
+
+namespace gd {
+
+constexpr int kMaxZClasses = 8;
+
+// Device view of one pooled scenario (all pointers into the pool arena).
+struct SceneDev {
+    const float4 *road_a;     // [Rpad] x, y, qw, qz
+    const float2 *road_b;     // [Rpad] d0, d1
+    const uint32_t *road_c;   // [Rpad] zclass | type << 8
+    const float4 *road_d;     // [Rpad] d2, yaw(heading), id, mapType   (row emission only)
+    const float4 *coll_cull;  // [Cpad] cx, cy, bounding radius, type
+    const float4 *coll_obb;   // [Cpad*4] corners(8) | axes(4) | origin(2) z dz
+    const float *traj;        // [A][1456]
+    const float4 *ag_a;       // [A] length, width, height, id
+    const float4 *ag_b;       // [A] d0, d1, d2, type
+    const float4 *ag_c;       // [A] goal.x, goal.y, responseType, controlled
+    const int4 *meta;         // [A]
+    float zc_z[kMaxZClasses];   // distinct (z, d2) pairs of the road entities
+    float zc_d2[kMaxZClasses];
+    int32_t numZClasses;
+    int32_t numRoads, numAgents, numColl;
+    float mean[3];
+    int32_t mapName[32];
+    int32_t scenarioId[32];
+};
+
+// Export buffers: reference AoS layouts, [world][slot]... (src/mgr.cpp:656-902)
+struct Exports {
+    float *action;        // [W,S,10]
+    float *reward;        // [W,S,1]
+    int32_t *done;        // [W,S,1]
+    int32_t *info;        // [W,S,5]
+    float *self_obs;      // [W,S,8]
+    float *abs_obs;       // [W,S,14]
+    float *partner_obs;   // [W,S,S-1,9]
+    float *agent_roadmap; // [W,S,200,9]
+    float *map_obs;       // [W,10000,9]
+    float *lidar;         // [W,S,3,50,4]
+    int32_t *steps_remaining; // [W,S,1]
+    int32_t *shape;       // [W,2]
+    int32_t *controlled;  // [W,S,1]
+    int32_t *response;    // [W,S,1]
+    float *traj;          // [W,S,1456]
+    float *world_means;   // [W,3]
+    int32_t *metadata;    // [W,S,4]
+    int32_t *deleted;     // [W,S]
+    int32_t *map_name;    // [W,32]
+    int32_t *scenario_id; // [W,32]
+    int32_t *valid_state; // [W,S,1] (never written by the reference)
+    int32_t *knn_idx;     // [W,S,200] debug side buffer: road-entity index per roadmap row, -1 pad
+};
+
+// Internal SoA agent state
+struct StateDev {
+    float4 *pos;          // [W,S] x, y, z, vz
+    float4 *rv;           // [W,S] qw, qz, vx, vy
+    int32_t *collided;    // [W,S] CollisionDetectionEvent.hasCollided
+    int32_t *world_scene; // [W]
+    int32_t *reset_flag;  // [W]
+    unsigned long long *stats; // [16] episode statistics accumulators
+};
+
+enum TensorId : int32_t {
+    T_ACTION = 0, T_REWARD, T_DONE, T_SELF_OBS, T_MAP_OBS, T_PARTNER_OBS, T_AGENT_ROADMAP, T_LIDAR,
+    T_BEV, T_STEPS_REMAINING, T_SHAPE, T_CONTROLLED, T_ABS_OBS, T_VALID_STATE, T_INFO, T_RESPONSE,
+    T_TRAJ, T_WORLD_MEANS, T_METADATA, T_DELETED, T_MAP_NAME, T_SCENARIO_ID, T_KNN_IDX, T_NUM
+};
+
+struct TensorDesc {
+    void *ptr;
+    int32_t dtype;   // 0 = f32, 1 = i32
+    int32_t ndim;
+    int64_t shape[8];
+    int32_t device;
+};
+
+struct StepStats {      // gd_stats
+    uint64_t steps;
+    uint64_t agent_steps;       // live agents x steps
+    uint64_t controlled_steps;  // live controlled agents x steps
+    uint64_t episodes_reset;
+    uint64_t collided_road, collided_vehicle, collided_nonvehicle, goals_reached, dones;
+};
+
+class Engine {
+public:
+    Engine(int gpu_id, int max_agents, const Params &params, const std::vector<std::string> &scenes);
+    ~Engine();
+
+    void step();                 // launch + sync (reference semantics, src/mgr.cpp:569-580)
+    void stepAsync();            // launch only, on stream()
+    void sync();
+    void reset(const int32_t *worlds, int n);
+    void setMaps(const std::vector<std::string> &scenes);
+    void deleteAgents(int world, const int32_t *ids, int n);
+    TensorDesc tensor(int id) const;
+    // e2e entry: actions from HOST memory, results to HOST memory, copies inside the call
+    void stepHost(const float *actions, int action_cols, float *reward, int32_t *done, int32_t *info);
+    // scenario pool (device auto-reset)
+    int poolAdd(const std::string &path);       // returns scene id
+    void bindWorlds(const int32_t *worlds, const int32_t *scene_ids, int n);   // + reset
+    StepStats stats();
+    cudaStream_t stream() const { return stream_; }
+    int numWorlds() const { return W_; }
+    int maxAgents() const { return S_; }
+    int lastKernelCount() const { return kernels_per_step_; }
+    uint64_t launches() const { return launches_; }
+
+private:
+    struct SceneHost {
+        std::string key;
+        SceneDev dev;
+        int32_t numAgents, numRoads, numControlled;
+    };
+    int sceneFor(const std::string &path, const std::vector<int32_t> &deleted);
+    int uploadScene(const SceneData &s, const std::string &key);
+    void *arenaAlloc(size_t bytes);
+    void syncSceneTable();
+    void launchBindReset(const std::vector<int32_t> &worlds, bool rebind);
+    void launchRest(bool decrement);
+    void allocExports();
+
+    int gpu_, W_, S_;
+    Params params_;
+    cudaStream_t stream_ = nullptr;
+    std::vector<std::string> scene_paths_;            // per world
+    std::vector<std::vector<int32_t>> deleted_;       // per world
+    std::vector<int32_t> world_scene_;                // per world -> scene id
+    std::vector<SceneHost> scenes_;
+    std::map<std::string, int> scene_index_;
+    std::map<std::string, std::shared_ptr<ParsedMap>> parsed_cache_;
+    SceneDev *d_scenes_ = nullptr;
+    size_t d_scenes_cap_ = 0;
+    bool scene_table_dirty_ = true;
+    std::vector<void *> arena_slabs_;
+    size_t arena_off_ = 0, arena_cap_ = 0;
+    int max_roads_ = 0;        // over the pool
+    Exports ex_{};
+    StateDev st_{};
+    std::vector<void *> owned_;
+    int32_t *d_worklist_ = nullptr;   // [W] scratch for reset lists
+    float *h_pinned_actions_ = nullptr;
+    int kernels_per_step_ = 0;
+    uint64_t launches_ = 0;
+    uint64_t steps_ = 0, episodes_reset_ = 0;
+};
+
+} // namespace gd

@@ -1,0 +1,153 @@
+/* C ABI of the B200-native GPUDrive step engine (libgpudrive_b200.so).
+ *
+ * Drop-in boundary for the path behind the reference's `madrona_gpudrive.SimManager`
+ * (nanobind class, src/bindings.cpp:91-149) / `Manager` (src/mgr.hpp:28-100). The reference has
+ * no C ABI; each entry point below names the Manager member it replaces. Plain pointers and
+ * sizes only; no torch / C++ types cross this boundary. Every call returns 0 on success and a
+ * non-zero code on failure, with the message available from gd_last_error() (the reference
+ * aborts the process instead: FATAL / assert / REQ_CUDA).
+ *
+ * Threading: one caller thread per handle. gd_step / gd_reset / gd_set_maps / gd_delete_agents
+ * return after the device is idle, as Manager::step does (external/madrona/src/mw/cuda_exec.cpp:1892).
+ * Tensor pointers are device pointers on GdConfig.gpu_id and stay valid for the handle's lifetime.
+ */
+#ifndef GPUDRIVE_B200_H
+#define GPUDRIVE_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* Parameters, src/init.hpp:111-127 (bool fields widened to int32). Enum values:
+ * rewardType 0 DistanceBased | 1 OnGoalAchieved | 2 Dense (src/init.hpp:76-81)
+ * collisionBehaviour 0 AgentStop | 1 AgentRemoved | 2 Ignore (:90-95)
+ * dynamicsModel 0 Classic | 1 InvertibleBicycle | 2 DeltaLocal | 3 State (:97-103)
+ * roadObservationAlgorithm 0 KNearestEntitiesWithRadiusFiltering | 1 AllEntitiesWithRadiusFiltering (:105-109) */
+typedef struct GdParams {
+    float polylineReductionThreshold;
+    float observationRadius;
+    int32_t rewardType;
+    float distanceToGoalThreshold;
+    float distanceToExpertThreshold;
+    int32_t collisionBehaviour;
+    uint32_t maxNumControlledAgents;
+    int32_t ignoreNonVehicles;
+    int32_t roadObservationAlgorithm;
+    int32_t initOnlyValidAgentsAtFirstStep;
+    int32_t isStaticAgentControlled;
+    int32_t enableLidar;
+    int32_t disableClassicalObs;
+    int32_t dynamicsModel;
+    int32_t readFromTracksToPredict;
+} GdParams;
+
+/* Manager::Config, src/mgr.hpp:30-44. max_agents is consts::kMaxAgentCount (src/consts.hpp:11),
+ * a constructor constant here: 128 reproduces the reference's tensor shapes. */
+typedef struct GdConfig {
+    int32_t gpu_id;
+    int32_t max_agents;
+    GdParams params;
+} GdConfig;
+
+typedef void *GdHandle;
+
+/* Tensor ids: one per SimManager getter (src/bindings.cpp:111-149, src/mgr.cpp:656-902). */
+enum GdTensorId {
+    GD_T_ACTION = 0,            /* action_tensor                    f32 [W,S,10]      (input) */
+    GD_T_REWARD,                /* reward_tensor                    f32 [W,S,1]       */
+    GD_T_DONE,                  /* done_tensor                      i32 [W,S,1]       */
+    GD_T_SELF_OBSERVATION,      /* self_observation_tensor          f32 [W,S,8]       */
+    GD_T_MAP_OBSERVATION,       /* map_observation_tensor           f32 [W,10000,9]   */
+    GD_T_PARTNER_OBSERVATIONS,  /* partner_observations_tensor      f32 [W,S,S-1,9]   */
+    GD_T_AGENT_ROADMAP,         /* agent_roadmap_tensor             f32 [W,S,200,9]   */
+    GD_T_LIDAR,                 /* lidar_tensor                     f32 [W,S,3,50,4]  */
+    GD_T_BEV_OBSERVATION,       /* bev_observation_tensor           (not built: returns an error) */
+    GD_T_STEPS_REMAINING,       /* steps_remaining_tensor           i32 [W,S,1]       */
+    GD_T_SHAPE,                 /* shape_tensor                     i32 [W,2]         */
+    GD_T_CONTROLLED_STATE,      /* controlled_state_tensor          i32 [W,S,1]       */
+    GD_T_ABSOLUTE_SELF_OBSERVATION, /* absolute_self_observation_tensor f32 [W,S,14]  */
+    GD_T_VALID_STATE,           /* valid_state_tensor               i32 [W,S,1] zeros */
+    GD_T_INFO,                  /* info_tensor                      i32 [W,S,5]       */
+    GD_T_RESPONSE_TYPE,         /* response_type_tensor             i32 [W,S,1]       */
+    GD_T_EXPERT_TRAJECTORY,     /* expert_trajectory_tensor         f32 [W,S,1456]    */
+    GD_T_WORLD_MEANS,           /* world_means_tensor               f32 [W,3]         */
+    GD_T_METADATA,              /* metadata_tensor                  i32 [W,S,4]       */
+    GD_T_DELETED_AGENTS,        /* deleted_agents_tensor            i32 [W,S]         */
+    GD_T_MAP_NAME,              /* map_name_tensor                  i32 [W,32]        */
+    GD_T_SCENARIO_ID,           /* scenario_id_tensor               i32 [W,32]        */
+    GD_T_KNN_INDEX,             /* (new) road-entity index of each agent_roadmap row, -1 pad: i32 [W,S,200] */
+    GD_T_COUNT
+};
+
+typedef struct GdTensorDesc {
+    void *ptr;          /* device pointer */
+    int32_t dtype;      /* 0 = float32, 1 = int32 */
+    int32_t ndim;
+    int64_t shape[8];   /* C-contiguous */
+    int32_t device;     /* CUDA device ordinal */
+} GdTensorDesc;
+
+typedef struct GdStats {
+    uint64_t steps;
+    uint64_t agent_steps;        /* live agents x steps */
+    uint64_t controlled_steps;   /* live controlled agents x steps */
+    uint64_t episodes_reset;
+    uint64_t collided_road, collided_vehicle, collided_nonvehicle, goals_reached, dones;
+} GdStats;
+
+/* Manager::Manager(cfg) — src/mgr.cpp:565 (Impl::init :399-563, then reset({})). num_worlds = n_scenes. */
+int gd_create(const GdConfig *cfg, const char *const *scenes, int32_t n_scenes, GdHandle *out);
+/* Manager::~Manager — src/mgr.cpp:567 */
+int gd_destroy(GdHandle h);
+/* Manager::step — src/mgr.cpp:569-580 */
+int gd_step(GdHandle h);
+/* Launch a step on the engine stream without waiting; pair with gd_sync (no reference equivalent). */
+int gd_step_async(GdHandle h);
+int gd_sync(GdHandle h);
+/* Manager::reset(worldsToReset) — src/mgr.cpp:582-588 (triggerReset :904-920 + Reset graph) */
+int gd_reset(GdHandle h, const int32_t *worlds, int32_t n);
+/* Manager::setMaps — src/mgr.cpp:590-654 */
+int gd_set_maps(GdHandle h, const char *const *scenes, int32_t n_scenes);
+/* Manager::deleteAgents — src/mgr.cpp:665-715 (one world per call) */
+int gd_delete_agents(GdHandle h, int32_t world, const int32_t *agent_ids, int32_t n);
+/* Manager::*Tensor() — src/mgr.cpp:656-902 */
+int gd_tensor(GdHandle h, int32_t tensor_id, GdTensorDesc *out);
+/* Host-buffer step: copies actions[W,S,action_cols] host->device into action_tensor[:, :, :action_cols],
+ * steps, copies reward / done / info (any may be NULL) device->host, then returns.
+ * Equivalent of the env's `action_tensor().copy_(a); sim.step(); reward.cpu()` round trip
+ * (gpudrive/env/env_torch.py:606-660). */
+int gd_step_host(GdHandle h, const float *actions, int32_t action_cols, float *reward, int32_t *done,
+                 int32_t *info);
+/* Device scenario pool: load a scenario once, re-bind worlds to pooled scenarios + reset them. */
+int gd_pool_add(GdHandle h, const char *scene_path, int32_t *scene_id_out);
+int gd_bind_worlds(GdHandle h, const int32_t *worlds, const int32_t *scene_ids, int32_t n);
+int gd_stats(GdHandle h, GdStats *out);
+int gd_num_worlds(GdHandle h);
+int gd_max_agents(GdHandle h);
+/* kernels launched since creation (bench.py's gpu_launches) */
+uint64_t gd_launch_count(GdHandle h);
+/* cudaStream_t the engine launches on (as an integer), for timing with CUDA events */
+uint64_t gd_stream(GdHandle h);
+const char *gd_last_error(void);
+
+/* Host-only scenario loader check (no GPU needed): parses a scenario and returns entity counts.
+ * Replaces MapReader::parseAndWriteOut + createPersistentEntities for inspection
+ * (src/MapReader.cpp:55-62, src/level_gen.cpp:396-465). */
+typedef struct GdSceneInfo {
+    int32_t num_agents, num_roads, num_controlled;
+    float mean[3];
+} GdSceneInfo;
+int gd_scene_info(const char *scene_path, const GdParams *params, int32_t max_agents, GdSceneInfo *out);
+/* Fills caller buffers with the host-built static tensors of one scenario (any pointer may be NULL):
+ * map_obs [num_roads,9], traj [num_agents,1456], agent_static [num_agents,16] =
+ * {length,width,height, scale d0,d1,d2, goal x,y, type, id, responseType, controlled, meta[4]}. */
+int gd_scene_tensors(const char *scene_path, const GdParams *params, int32_t max_agents,
+                     float *map_obs, int32_t map_rows_cap, float *traj, float *agent_static,
+                     int32_t agent_cap);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GPUDRIVE_B200_H */
