@@ -7,6 +7,9 @@
 #include <string>
 #include <vector>
 #include <dlfcn.h>
+#include <execinfo.h>
+#include <signal.h>
+#include <unistd.h>
 
 using namespace madrona_gpudrive;
 
@@ -25,7 +28,28 @@ std::string gd_ref_data_dir()
     return "oracle/ref/assets/";
 }
 
+static void gd_ref_segv(int sig)
+{
+    void *frames[64];
+    int n = backtrace(frames, 64);
+    const char msg[] = "gd_ref: fatal signal, backtrace:\n";
+    (void)!write(2, msg, sizeof(msg) - 1);
+    backtrace_symbols_fd(frames, n, 2);
+    _exit(128 + sig);
+}
+
 extern "C" {
+
+// Debug aid: GD_REF_BACKTRACE=1 prints a native backtrace on SIGSEGV/SIGABRT.
+void gd_ref_install_backtrace(void)
+{
+    static char altstack[1 << 16];
+    stack_t ss; ss.ss_sp = altstack; ss.ss_size = sizeof(altstack); ss.ss_flags = 0;
+    sigaltstack(&ss, nullptr);
+    struct sigaction sa; memset(&sa, 0, sizeof(sa));
+    sa.sa_handler = gd_ref_segv; sa.sa_flags = SA_ONSTACK;
+    sigaction(SIGSEGV, &sa, nullptr); sigaction(SIGABRT, &sa, nullptr);
+}
 
 // Mirrors Parameters (src/init.hpp:111-127) field by field.
 struct GdRefParams {
