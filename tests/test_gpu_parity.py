@@ -1,0 +1,108 @@
+"""-m gpu: parity of the CUDA step engine against the reference's own CPU Manager (oracle/_ref)
+on identical synthetic scenes and actions, through the C ABI. Bit-exact: done / info / collision
+flags / ids / partner ordering / roadmap index sets. 1e-5 relative: positions, headings, speeds,
+observations, lidar depths, rewards (rules in helpers.compare_step)."""
+import numpy as np
+import pytest
+
+from helpers import param_dict
+from rollout import run_parity
+
+pytestmark = pytest.mark.gpu
+
+
+def _need():
+    import torch
+    if not torch.cuda.is_available():
+        pytest.fail("CUDA device required for -m gpu tests (no CPU fallback exists)")
+    from oracle import refmgr
+    if not refmgr.available():
+        pytest.fail("oracle/_ref/libgd_ref.so missing: run __graft_entry__.build() where /root/reference exists")
+
+
+def _scenes(synth_dir, n, **kw):
+    from gpudrive_lab_b200 import synth
+    return synth.write_scenarios(synth_dir, n, **kw)
+
+
+def test_bicycle_ignore_full_episode(synth_dir):
+    """config 2 shape: InvertibleBicycle, self + partner + roadmap, 91 steps."""
+    _need()
+    scenes = _scenes(synth_dir, 2)
+    pd = param_dict(dynamicsModel=1, collisionBehaviour=2)
+    _, _, stats = run_parity(scenes, pd, 91)
+    assert stats.get("knn_boundary_ties", 0) <= 1e-3 * stats["knn_agents"]
+
+
+def test_delta_lidar_full_episode(synth_dir):
+    """config 3 shape: DeltaLocal, full observations + lidar, 91 steps."""
+    _need()
+    scenes = _scenes(synth_dir, 2)
+    pd = param_dict(dynamicsModel=2, enableLidar=True)
+    _, _, stats = run_parity(scenes, pd, 91)
+    assert stats["lidar_mismatch"] <= 1e-4 * stats["lidar_rays"]
+
+
+def test_agent_stop_collisions(synth_dir):
+    """AgentStop: collided agents freeze, then get removed; flags must stay bit-exact."""
+    _need()
+    scenes = _scenes(synth_dir, 2, stress=True)
+    pd = param_dict(dynamicsModel=1, collisionBehaviour=0, enableLidar=True)
+    ref, sim, _ = run_parity(scenes, pd, 91)
+    info = ref.tensor("info")
+    assert info[..., :3].sum() > 0, "the stress scene is expected to produce collisions"
+
+
+def test_agent_removed_classic(synth_dir):
+    _need()
+    scenes = _scenes(synth_dir, 1, stress=True)
+    pd = param_dict(dynamicsModel=0, collisionBehaviour=1)
+    run_parity(scenes, pd, 60)
+
+
+def test_expert_replay_linear_roadmap(synth_dir):
+    """No controlled agents (pure expert replay, tests/test_expert.py) + the env-default 'linear'
+    road algorithm (AllEntitiesWithRadiusFiltering)."""
+    _need()
+    scenes = _scenes(synth_dir, 2)
+    pd = param_dict(dynamicsModel=1, maxNumControlledAgents=0, roadObservationAlgorithm=1,
+                    collisionBehaviour=0, isStaticAgentControlled=False)
+    run_parity(scenes, pd, 91)
+
+
+def test_state_model_and_distance_reward(synth_dir):
+    _need()
+    scenes = _scenes(synth_dir, 1)
+    pd = param_dict(dynamicsModel=3, rewardType=0, observationRadius=30.0)
+    run_parity(scenes, pd, 10)
+
+
+def test_reset_and_partial_reset(synth_dir):
+    _need()
+    import torch
+    scenes = _scenes(synth_dir, 3)
+    pd = param_dict(dynamicsModel=1, enableLidar=True)
+    from helpers import compare_step, snapshot_engine, snapshot_ref
+    ref, sim, _ = run_parity(scenes, pd, 12)
+    ref.reset([1]); sim.reset([1])
+    compare_step(snapshot_ref(ref), snapshot_engine(sim), 50.0, True, tag="after reset([1])")
+    assert int(sim.steps_remaining_tensor().to_torch()[1, 0, 0]) == 91
+    assert int(sim.steps_remaining_tensor().to_torch()[0, 0, 0]) == 91 - 12
+    ref.step(); sim.step()
+    compare_step(snapshot_ref(ref), snapshot_engine(sim), 50.0, True, tag="step after reset")
+
+
+def test_set_maps_and_delete_agents(synth_dir):
+    _need()
+    from helpers import compare_step, snapshot_engine, snapshot_ref
+    scenes = _scenes(synth_dir, 4)
+    pd = param_dict(dynamicsModel=2)
+    ref, sim, _ = run_parity(scenes[:2], pd, 5)
+    ref.set_maps(scenes[2:4]); sim.set_maps(scenes[2:4])
+    compare_step(snapshot_ref(ref), snapshot_engine(sim), 50.0, False, tag="after set_maps")
+    ids = [100, 103, 117]
+    ref.delete_agents(1, ids); sim.deleteAgents({1: ids})
+    compare_step(snapshot_ref(ref), snapshot_engine(sim), 50.0, False, tag="after deleteAgents")
+    assert int(sim.shape_tensor().to_torch()[1, 0]) == 61
+    ref.step(); sim.step()
+    compare_step(snapshot_ref(ref), snapshot_engine(sim), 50.0, False, tag="step after deleteAgents")
