@@ -10,7 +10,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OUT = os.path.join(HERE, "libgpudrive_b200.so")
 SOURCES = ["engine.cu", "scenario.cpp", "capi.cpp"]
-HEADERS = ["engine.h", "gd_types.h", "scenario.h", "json_min.h", "device_math.cuh", "kernels_step.cuh",
+HEADERS = ["engine.h", "gd_types.h", "scenario.h", "json_min.h", "glibc_trig.h", "device_math.cuh", "kernels_step.cuh",
            "kernels_obs.cuh", "kernels_reset.cuh", os.path.join("..", "..", "include", "gpudrive_b200.h")]
 
 NVCC_FLAGS = [

@@ -7,15 +7,22 @@
 #pragma once
 #include <cuda_runtime.h>
 #include "gd_types.h"
+#include "glibc_trig.h"
 
 namespace gd {
 
-// Per-agent trigonometry goes through fp64 and is rounded once: (float)cos((double)x) is the
-// correctly rounded cosf(x) in all but ~1e-8 of cases, which is what glibc's cosf/sinf/atan2
-// return for >99% of inputs. This keeps per-agent state within a few ulp of the CPU reference
-// over a 91-step rollout. It runs once per agent per step, never per road entity.
-__device__ __forceinline__ float cos_hp(float x) { return (float)cos((double)x); }
-__device__ __forceinline__ float sin_hp(float x) { return (float)sin((double)x); }
+// Per-agent trigonometry. sinf / cosf reproduce glibc's results bit for bit (glibc_trig.h); the
+// remaining functions go through fp64 and are rounded once: (float)atan2((double)y, (double)x) is
+// what the reference's g++ build computes (its unqualified atan2 / fmod bind to the double
+// overloads), and fp64 tan / atan rounded to float equal glibc's tanf / atanf for all but a
+// vanishing fraction of inputs (Classic model only). These run once per agent per step, never
+// per road entity.
+__device__ __forceinline__ float cos_hp(float x) {
+    return gdtrig::in_fast_range(x) ? gdtrig::cosf_glibc(x) : (float)cos((double)x);
+}
+__device__ __forceinline__ float sin_hp(float x) {
+    return gdtrig::in_fast_range(x) ? gdtrig::sinf_glibc(x) : (float)sin((double)x);
+}
 __device__ __forceinline__ float tan_hp(float x) { return (float)tan((double)x); }
 __device__ __forceinline__ float atan_hp(float x) { return (float)atan((double)x); }
 __device__ __forceinline__ float atan2_hp(float y, float x) { return (float)atan2((double)y, (double)x); }

@@ -275,7 +275,7 @@ k_obs(const SceneDev *__restrict__ scenes, StateDev st, Exports ex, Params prm, 
         for (int i = lane; i < NRAY; i += 32) {
             const float theta = __fadd_rn(__fmul_rn(kLidarAngle,
                 __fsub_rn(__fdiv_rn(2.f * (float)i, (float)NRAY), 1.f)), head);
-            const float x = cosf(theta), y = sinf(theta);
+            const float x = cos_hp(theta), y = sin_hp(theta);      // sim.cpp:411-412
             const float dx = __fadd_rn(__fmul_rn(x, rgx), __fmul_rn(y, fwx));
             const float dy = __fadd_rn(__fmul_rn(x, rgy), __fmul_rn(y, fwy));
             const float inv = __fdiv_rn(1.f, __fsqrt_rn(__fadd_rn(len2_xy(dx, dy), 0.f)));
