@@ -53,7 +53,7 @@ EXPORTED_SYMBOLS = [
     "gd_create", "gd_destroy", "gd_step", "gd_step_async", "gd_sync", "gd_reset", "gd_set_maps",
     "gd_delete_agents", "gd_tensor", "gd_step_host", "gd_pool_add", "gd_bind_worlds", "gd_stats",
     "gd_num_worlds", "gd_max_agents", "gd_launch_count", "gd_stream", "gd_last_error",
-    "gd_scene_info", "gd_scene_tensors",
+    "gd_scene_info", "gd_scene_tensors", "gd_set_option", "gd_kernel_times",
 ]
 
 TENSOR_IDS = {
@@ -92,6 +92,8 @@ def load():
     lib.gd_pool_add.argtypes = [H, C.c_char_p, C.POINTER(C.c_int32)]
     lib.gd_bind_worlds.argtypes = [H, C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.c_int32]
     lib.gd_stats.argtypes = [H, C.POINTER(GdStats)]
+    lib.gd_set_option.argtypes = [H, C.c_int32, C.c_int32]
+    lib.gd_kernel_times.argtypes = [H, C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(C.c_int64)]
     lib.gd_num_worlds.argtypes = [H]
     lib.gd_max_agents.argtypes = [H]
     lib.gd_launch_count.argtypes = [H]

@@ -96,6 +96,10 @@ int gd_stats(GdHandle h, GdStats *out) {
     })
 }
 
+int gd_set_option(GdHandle h, int32_t option, int32_t value) { GD_TRY({ E(h)->setOption(option, value); }) }
+int gd_kernel_times(GdHandle h, double *agents_ms, double *obs_ms, int64_t *steps) {
+    GD_TRY({ E(h)->kernelTimes(agents_ms, obs_ms, steps); })
+}
 int gd_num_worlds(GdHandle h) { return h ? static_cast<gd::Engine *>(h)->numWorlds() : -1; }
 int gd_max_agents(GdHandle h) { return h ? static_cast<gd::Engine *>(h)->maxAgents() : -1; }
 uint64_t gd_launch_count(GdHandle h) { return h ? static_cast<gd::Engine *>(h)->launches() : 0; }

@@ -70,6 +70,7 @@ Engine::Engine(int gpu_id, int max_agents, const Params &params, const std::vect
 Engine::~Engine() {
     cudaSetDevice(gpu_);
     cudaDeviceSynchronize();
+    for (auto &e : prof_ev_) cudaEventDestroy(e);
     for (void *p : owned_) cudaFree(p);
     for (void *p : arena_slabs_) cudaFree(p);
     if (d_scenes_) cudaFree(d_scenes_);
@@ -291,10 +292,20 @@ void Engine::launchBindReset(const std::vector<int32_t> &worlds, bool rebind) {
 void Engine::launchRest(bool decrement) {
     syncSceneTable();
     const size_t smem_agents = sizeof(AgentBox) * (size_t)S_;
+    const bool prof = opt_profile_ && decrement;
+    cudaEvent_t *ev = nullptr;
+    if (prof) {
+        if (prof_pending_ == kProfRing) foldProfile();
+        ev = &prof_ev_[3 * prof_pending_];
+        GD_CUDA(cudaEventRecord(ev[0], stream_));
+    }
     k_agents<AGENTS_BLOCK><<<W_, AGENTS_BLOCK, smem_agents, stream_>>>(d_scenes_, st_, ex_, params_, S_,
                                                                     decrement ? 1 : 0, decrement ? 1 : 0);
+    if (prof) GD_CUDA(cudaEventRecord(ev[1], stream_));
     const int groups = (S_ + OBS_WARPS - 1) / OBS_WARPS;
-    k_obs<<<W_ * groups, OBS_BLOCK, sizeof(ObsSmem), stream_>>>(d_scenes_, st_, ex_, params_, S_, groups, 1);
+    k_obs<<<W_ * groups, OBS_BLOCK, sizeof(ObsSmem), stream_>>>(d_scenes_, st_, ex_, params_, S_, groups,
+                                                                opt_knn_idx_);
+    if (prof) { GD_CUDA(cudaEventRecord(ev[2], stream_)); prof_pending_++; }
     launches_ += 2;
     kernels_per_step_ = 2;
     GD_CUDA(cudaGetLastError());
@@ -407,6 +418,38 @@ void Engine::stepHost(const float *actions, int action_cols, float *reward, int3
     if (done) GD_CUDA(cudaMemcpyAsync(done, ex_.done, WS * sizeof(int32_t), cudaMemcpyDeviceToHost, stream_));
     if (info) GD_CUDA(cudaMemcpyAsync(info, ex_.info, WS * kInfoSize * sizeof(int32_t), cudaMemcpyDeviceToHost, stream_));
     sync();
+}
+
+void Engine::setOption(int option, int value) {
+    if (option == 0) opt_knn_idx_ = value ? 1 : 0;
+    else if (option == 1) {
+        GD_CUDA(cudaSetDevice(gpu_));
+        if (value && prof_ev_.empty()) {
+            prof_ev_.resize(3 * kProfRing);
+            for (auto &e : prof_ev_) GD_CUDA(cudaEventCreate(&e));
+        }
+        if (value && !opt_profile_) { prof_pending_ = 0; prof_agents_ms_ = prof_obs_ms_ = 0; prof_steps_ = 0; }
+        opt_profile_ = value ? 1 : 0;
+    } else throw std::runtime_error("unknown option");
+}
+
+void Engine::foldProfile() {
+    if (!prof_pending_) return;
+    GD_CUDA(cudaEventSynchronize(prof_ev_[3 * (prof_pending_ - 1) + 2]));
+    for (int i = 0; i < prof_pending_; i++) {
+        float a = 0, o = 0;
+        GD_CUDA(cudaEventElapsedTime(&a, prof_ev_[3 * i], prof_ev_[3 * i + 1]));
+        GD_CUDA(cudaEventElapsedTime(&o, prof_ev_[3 * i + 1], prof_ev_[3 * i + 2]));
+        prof_agents_ms_ += a; prof_obs_ms_ += o;
+    }
+    prof_steps_ += prof_pending_;
+    prof_pending_ = 0;
+}
+
+void Engine::kernelTimes(double *agents_ms, double *obs_ms, int64_t *steps) {
+    GD_CUDA(cudaSetDevice(gpu_));
+    foldProfile();
+    *agents_ms = prof_agents_ms_; *obs_ms = prof_obs_ms_; *steps = prof_steps_;
 }
 
 StepStats Engine::stats() {

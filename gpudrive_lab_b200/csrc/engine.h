@@ -115,6 +115,10 @@ public:
     int poolAdd(const std::string &path);       // returns scene id
     void bindWorlds(const int32_t *worlds, const int32_t *scene_ids, int n);   // + reset
     StepStats stats();
+    // options: 0 = write the knn index side buffer (default 1), 1 = per-kernel CUDA-event timing (default 0)
+    void setOption(int option, int value);
+    // accumulated device time of the two step kernels since profiling was switched on (ms) and the step count
+    void kernelTimes(double *agents_ms, double *obs_ms, int64_t *steps);
     cudaStream_t stream() const { return stream_; }
     int numWorlds() const { return W_; }
     int maxAgents() const { return S_; }
@@ -158,6 +162,13 @@ private:
     int kernels_per_step_ = 0;
     uint64_t launches_ = 0;
     uint64_t steps_ = 0, episodes_reset_ = 0;
+    int opt_knn_idx_ = 1, opt_profile_ = 0;
+    static constexpr int kProfRing = 64;
+    std::vector<cudaEvent_t> prof_ev_;      // 3 events per ring slot
+    int prof_pending_ = 0;                  // slots recorded, not yet folded into the sums
+    double prof_agents_ms_ = 0, prof_obs_ms_ = 0;
+    int64_t prof_steps_ = 0;
+    void foldProfile();
 };
 
 } // namespace gd

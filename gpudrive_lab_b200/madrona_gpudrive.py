@@ -215,6 +215,14 @@ class SimManager:
         _capi.check(self._lib.gd_stats(self._h, C.byref(s)))
         return {n: int(getattr(s, n)) for n, _ in s._fields_}
 
+    def set_option(self, option: int, value: int):
+        _capi.check(self._lib.gd_set_option(self._h, int(option), int(value)))
+
+    def kernel_times(self) -> dict:
+        a, o, n = C.c_double(), C.c_double(), C.c_int64()
+        _capi.check(self._lib.gd_kernel_times(self._h, C.byref(a), C.byref(o), C.byref(n)))
+        return {"k_agents_ms": a.value, "k_obs_ms": o.value, "steps": n.value}
+
     def launch_count(self) -> int:
         return int(self._lib.gd_launch_count(self._h))
 

@@ -124,6 +124,12 @@ int gd_step_host(GdHandle h, const float *actions, int32_t action_cols, float *r
 int gd_pool_add(GdHandle h, const char *scene_path, int32_t *scene_id_out);
 int gd_bind_worlds(GdHandle h, const int32_t *worlds, const int32_t *scene_ids, int32_t n);
 int gd_stats(GdHandle h, GdStats *out);
+/* Engine options (no reference equivalent): GD_OPT_KNN_INDEX (default 1) writes the GD_T_KNN_INDEX side
+ * buffer; GD_OPT_PROFILE (default 0) brackets the two step kernels with CUDA events on the engine stream. */
+enum GdOption { GD_OPT_KNN_INDEX = 0, GD_OPT_PROFILE = 1 };
+int gd_set_option(GdHandle h, int32_t option, int32_t value);
+/* Accumulated device time (ms) of k_agents / k_obs over the steps taken since GD_OPT_PROFILE was enabled. */
+int gd_kernel_times(GdHandle h, double *agents_ms, double *obs_ms, int64_t *steps);
 int gd_num_worlds(GdHandle h);
 int gd_max_agents(GdHandle h);
 /* kernels launched since creation (bench.py's gpu_launches) */
