@@ -7,7 +7,7 @@
 #include <cstring>
 #include <stdexcept>
 
-#include "kernels_obs.cuh"
+#include "kernels_obs_main.cuh"
 #include "kernels_reset.cuh"
 #include "kernels_step.cuh"
 
@@ -50,6 +50,15 @@ Engine::Engine(int gpu_id, int max_agents, const Params &params, const std::vect
     GD_CUDA(cudaStreamCreateWithFlags(&stream_, cudaStreamNonBlocking));
 
     allocExports();
+
+    // largest float key with sqrtf(key) <= observationRadius (exact stand-in for `length() <= radius`)
+    {
+        const float r = params_.observationRadius;
+        float k = r * r;
+        while (sqrtf(nextafterf(k, INFINITY)) <= r) k = nextafterf(k, INFINITY);
+        while (k > 0.f && sqrtf(k) > r) k = nextafterf(k, -INFINITY);
+        key_thr_ = (r >= 0.f) ? k : -1.f;
+    }
 
     scene_paths_ = scenes;
     deleted_.assign(W_, {});
@@ -304,7 +313,7 @@ void Engine::launchRest(bool decrement) {
     if (prof) GD_CUDA(cudaEventRecord(ev[1], stream_));
     const int groups = (S_ + OBS_WARPS - 1) / OBS_WARPS;
     k_obs<<<W_ * groups, OBS_BLOCK, sizeof(ObsSmem), stream_>>>(d_scenes_, st_, ex_, params_, S_, groups,
-                                                                opt_knn_idx_);
+                                                                opt_knn_idx_, key_thr_);
     if (prof) { GD_CUDA(cudaEventRecord(ev[2], stream_)); prof_pending_++; }
     launches_ += 2;
     kernels_per_step_ = 2;

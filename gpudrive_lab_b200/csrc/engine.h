@@ -163,6 +163,7 @@ private:
     uint64_t launches_ = 0;
     uint64_t steps_ = 0, episodes_reset_ = 0;
     int opt_knn_idx_ = 1, opt_profile_ = 0;
+    float key_thr_ = 0.f;
     static constexpr int kProfRing = 64;
     std::vector<cudaEvent_t> prof_ev_;      // 3 events per ring slot
     int prof_pending_ = 0;                  // slots recorded, not yet folded into the sums

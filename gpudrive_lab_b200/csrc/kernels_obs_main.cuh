@@ -1,0 +1,389 @@
+// k_obs kernel body (helpers in kernels_obs.cuh).
+#pragma once
+#include "kernels_obs.cuh"
+
+namespace gd {
+
+// key_thr: largest float k with sqrtf(k) <= observationRadius, so `key <= key_thr` is exactly the
+// reference's `length() <= radius` (knn.hpp:88, sim.cpp:268-271) without a square root per entity.
+__global__ void __launch_bounds__(OBS_BLOCK, 1)
+k_obs(const SceneDev *__restrict__ scenes, StateDev st, Exports ex, Params prm, int S, int groups,
+      int write_knn_idx, float key_thr)
+{
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    ObsSmem &sm = *reinterpret_cast<ObsSmem *>(smem_raw);
+
+    const int w = blockIdx.x / groups;
+    const int g = blockIdx.x % groups;
+    const SceneDev &sc = scenes[st.world_scene[w]];
+    const int A = sc.numAgents, R = sc.numRoads;
+    if (g * OBS_WARPS >= A) return;
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const unsigned FULL = 0xffffffffu;
+    const unsigned lt_mask = (1u << lane) - 1u;
+
+    // ---- stage the world's agents
+    for (int j = tid; j < A; j += OBS_BLOCK) {
+        const size_t wj = (size_t)w * S + j;
+        const float4 p = st.pos[wj], rv = st.rv[wj];
+        const float4 ga = sc.ag_a[j], gb = sc.ag_b[j];
+        sm.a0[j] = make_float4(p.x, p.y, rv.x, rv.y);
+        sm.a1[j] = make_float4(p.z, len3(rv.z, rv.w, p.w), gb.w, ga.w);
+    }
+    __syncthreads();
+
+    const int a = g * OBS_WARPS + warp;
+    const bool active = a < A;            // inactive warps still take part in the tile barriers
+    ObsWarpSmem &wp = sm.wp[warp];
+    const size_t wa = (size_t)w * S + (active ? a : 0);
+
+    float px = 0, py = 0, pz = 0, qw = 1, qz = 0;
+    if (active) {
+        const float4 s0 = sm.a0[a];
+        px = s0.x; py = s0.y; qw = s0.z; qz = s0.w; pz = sm.a1[a].x;
+    }
+    const float radius = prm.observationRadius;
+    const bool classical = !prm.disableClassicalObs;
+    const bool lidar_on = prm.enableLidar != 0;
+
+    // ------------------------------------------------------------ self + absolute observations
+    if (active && lane == 0) {
+        const float4 s1 = sm.a1[a], s3 = sc.ag_a[a];
+        const float4 gc = sc.ag_c[a];
+        float gx, gy;
+        inv_rotate_xy(qw, qz, __fsub_rn(gc.x, px), __fsub_rn(gc.y, py), gx, gy);
+        float4 *so = reinterpret_cast<float4 *>(ex.self_obs + wa * kSelfObsSize);
+        so[0] = make_float4(s1.y, s3.x, s3.y, s3.z);
+        so[1] = make_float4(gx, gy, st.collided[wa] ? 1.f : 0.f, s1.w);
+        float2 *ab = reinterpret_cast<float2 *>(ex.abs_obs + wa * kAbsObsSize);
+        ab[0] = make_float2(px, py);
+        ab[1] = make_float2(pz, qw);
+        ab[2] = make_float2(0.f * qz, 0.f * qz);            // Quat x, y = normal.{x,y} * sinhalf
+        ab[3] = make_float2(qz, quat_to_yaw_hp(qw, qz));
+        ab[4] = make_float2(gc.x, gc.y);
+        ab[5] = make_float2(s3.x, s3.y);
+        ab[6] = make_float2(s3.z, s1.w);
+    }
+
+    // ------------------------------------------------------------ partner observations
+    if (active && classical) {
+        const int P = S - 1;
+        float *dstbase = ex.partner_obs + wa * P * kPartnerObsSize;
+        for (int base = 0; base < P; base += 32) {
+            const int jp = base + lane;
+            const bool has = jp < P;
+            float row[9];
+            if (has && jp < A - 1) {
+                const int j = jp < a ? jp : jp + 1;       // OtherAgents order, level_gen.cpp:450-464
+                const float4 o0 = sm.a0[j], o1 = sm.a1[j];
+                float rx, ry;
+                inv_rotate_xy(qw, qz, __fsub_rn(o0.x, px), __fsub_rn(o0.y, py), rx, ry);
+                if (__fsqrt_rn(len2_xy(rx, ry)) > radius) {
+                    row[0] = row[1] = row[2] = row[3] = row[4] = row[5] = row[6] = row[7] = 0.f;
+                    row[8] = -1.f;                          // PartnerObservation::zero()
+                } else {
+                    const float4 o3 = sc.ag_a[j];
+                    float rw, rz;
+                    inv_mul_quat(qw, qz, o0.z, o0.w, rw, rz);
+                    row[0] = o1.y; row[1] = rx; row[2] = ry; row[3] = quat_to_yaw(rw, rz);
+                    row[4] = o3.x; row[5] = o3.y; row[6] = o3.z; row[7] = o1.z; row[8] = o1.w;
+                }
+            } else {
+                row[0] = row[1] = row[2] = row[3] = row[4] = row[5] = row[6] = row[7] = 0.f;
+                row[8] = -2.f;                              // zero_nonexist()
+            }
+            const int m = min(32, P - base);
+            flush_rows(wp.u.stage, dstbase + (size_t)base * 9, row, has, lane, m, lane);
+        }
+    }
+
+    // ------------------------------------------------------------ lidar set-up
+    LidarCtx lc;
+    lc.ox = px; lc.oy = py; lc.fc = 1.f; lc.fs = 0.f; lc.head = 0; lc.tail = 0; lc.tile_base = 0;
+    int zmask_classes = 0;         // 3 bits per z-class
+    if (active && lidar_on) {
+        __syncwarp();
+        for (int i = lane; i < 3 * NRAY; i += 32) wp.u.best[i] = LIDAR_NONE;
+        const int controlled = ex.controlled[wa];
+        const float head = controlled ? ex.action[wa * kActionSize + 2] : 0.f;   // sim.cpp:409
+        float rgx, rgy, fwx, fwy;
+        rotate_xy(qw, qz, 1.f, 0.f, rgx, rgy);     // rot.rotateVec(math::right)
+        rotate_xy(qw, qz, 0.f, 1.f, fwx, fwy);     // rot.rotateVec(math::fwd)
+        for (int i = lane; i < NRAY; i += 32) {
+            const float theta = __fadd_rn(__fmul_rn(kLidarAngle,
+                __fsub_rn(__fdiv_rn(2.f * (float)i, (float)NRAY), 1.f)), head);
+            const float x = cos_hp(theta), y = sin_hp(theta);      // sim.cpp:411-412
+            const float dx = __fadd_rn(__fmul_rn(x, rgx), __fmul_rn(y, fwx));
+            const float dy = __fadd_rn(__fmul_rn(x, rgy), __fmul_rn(y, fwy));
+            const float inv = __fdiv_rn(1.f, __fsqrt_rn(__fadd_rn(len2_xy(dx, dy), 0.f)));
+            wp.raydir[i] = make_float2(__fmul_rn(dx, inv), __fmul_rn(dy, inv));
+            wp.rayxy[i] = make_float2(x, y);
+        }
+        const float yaw = quat_to_yaw(qw, qz);
+        const float delta = (2.f * kLidarAngle) / (float)NRAY;
+        const float mid = yaw + head - kLidarAngle + 0.5f * (float)(NRAY - 1) * delta;
+        sincosf(mid, &lc.fs, &lc.fc);
+        for (int c = 0; c < sc.numZClasses; c++)
+            zmask_classes |= plane_mask(pz, sc.zc_z[c], sc.zc_d2[c], -1.f, 1.f) << (3 * c);
+        __syncwarp();
+        // other agents first: few boxes, and their hits prune the road sweep on the edge plane
+        for (int base = 0; base < A; base += 32) {
+            const int j = base + lane;
+            unsigned long long m = 0ull; int ilo = 0; int pm = 0;
+            if (j < A) {
+                const float4 o0 = sm.a0[j]; const float4 gb = sc.ag_b[j];
+                pm = plane_mask(pz, sm.a1[j].x, gb.z, 0.f, 2.f);
+                if (pm) m = lidar_consider(lc, wp.u.best, pm, o0.x, o0.y, o0.z, o0.w, gb.x, gb.y, ilo);
+            }
+            lidar_push(sm, sc, wp, lc, lane, m, ilo, make_item(j, true, 0, pm));
+        }
+        lidar_drain(sm, sc, wp, lc, lane, true);
+    }
+
+    // ------------------------------------------------------------ road tiles: kNN candidates + lidar
+    int cnt = 0;                   // in-radius entities seen so far (warp-uniform)
+    const bool want_cands = active && classical;
+    const bool first_k_only = prm.roadObservationAlgorithm == RO_AllEntities;
+    const bool need_keys = want_cands || (active && lidar_on);
+    const float rpad = radius * 1.00001f + 1e-3f;      // |dx|,|dy| beyond this cannot be in radius
+    for (int t0 = 0; t0 < R; t0 += OBS_TILE) {
+        const int tl = min(OBS_TILE, R - t0);
+        __syncthreads();
+        for (int i = tid; i < tl; i += OBS_BLOCK) {
+            sm.ta[i] = sc.road_a[t0 + i];
+            sm.tb[i] = sc.road_b[t0 + i];
+            sm.tc[i] = sc.road_c[t0 + i];
+        }
+        __syncthreads();
+        if (!active || !need_keys) continue;
+        lc.tile_base = t0;
+        // ---- sweep 1: exact keys of nearby entities -> candidates; their boxes feed the lidar first
+        for (int base = 0; base < tl; base += 32) {
+            const int r = base + lane;
+            const bool valid = r < tl;
+            float4 ra = make_float4(0, 0, 1, 0);
+            bool nearb = false;
+            float dx = 0, dy = 0;
+            if (valid) {
+                ra = sm.ta[r];
+                dx = __fsub_rn(ra.x, px); dy = __fsub_rn(ra.y, py);
+                nearb = fabsf(dx) <= rpad && fabsf(dy) <= rpad;
+            }
+            unsigned inm = 0;
+            if (__any_sync(FULL, nearb)) {
+                bool in = false;
+                float key = 0.f;
+                if (nearb) {
+                    float ox, oy;
+                    inv_rotate_xy(qw, qz, dx, dy, ox, oy);
+                    key = len2_xy(ox, oy);
+                    in = key <= key_thr;
+                }
+                inm = __ballot_sync(FULL, in);
+                if (want_cands) {
+                    if (in) {
+                        const int pos = cnt + __popc(inm & lt_mask);
+                        if (pos < OBS_CAND) { wp.ckey[pos] = key; wp.cidx[pos] = (uint16_t)(t0 + r); }
+                    }
+                    cnt += __popc(inm);
+                }
+                if (lidar_on && inm) {
+                    unsigned long long m = 0ull; int ilo = 0; int pm = 0;
+                    if (in) {
+                        const uint32_t c = sm.tc[r];
+                        pm = (zmask_classes >> (3 * (c & 0xff))) & 7;
+                        if (pm) {
+                            const float2 rb = sm.tb[r];
+                            m = lidar_consider(lc, wp.u.best, pm, ra.x, ra.y, ra.z, ra.w, rb.x, rb.y, ilo);
+                        }
+                    }
+                    lidar_push(sm, sc, wp, lc, lane, m, ilo, make_item(r, false, 0, pm));
+                }
+            }
+            if (lidar_on && lane == 0) wp.inmask[base >> 5] = inm;
+        }
+        if (!lidar_on) continue;
+        lidar_drain(sm, sc, wp, lc, lane, true);
+        __syncwarp();
+        // ---- sweep 2: the far boxes, culled by cone / range / closest hit so far
+        for (int base = 0; base < tl; base += 32) {
+            const int r = base + lane;
+            const unsigned inm = wp.inmask[base >> 5];
+            unsigned long long m = 0ull; int ilo = 0; int pm = 0;
+            if (r < tl && !((inm >> lane) & 1u)) {
+                const uint32_t c = sm.tc[r];
+                pm = (zmask_classes >> (3 * (c & 0xff))) & 7;
+                if (pm) {
+                    const float4 ra = sm.ta[r]; const float2 rb = sm.tb[r];
+                    m = lidar_consider(lc, wp.u.best, pm, ra.x, ra.y, ra.z, ra.w, rb.x, rb.y, ilo);
+                }
+            }
+            lidar_push(sm, sc, wp, lc, lane, m, ilo, make_item(r, false, 0, pm));
+        }
+        lidar_drain(sm, sc, wp, lc, lane, true);   // items index this tile: finish before it is replaced
+    }
+    if (!active) return;
+
+    // ------------------------------------------------------------ lidar write-out
+    if (lidar_on) {
+        __syncwarp();
+        float4 *out = reinterpret_cast<float4 *>(ex.lidar + wa * 3 * NRAY * kLidarRowSize);
+        for (int i = lane; i < 3 * NRAY; i += 32) {
+            const unsigned long long b = wp.u.best[i];
+            float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (b != LIDAR_NONE) {
+                float t = __uint_as_float((unsigned)(b >> 32));
+                const unsigned id = (unsigned)(b & 0xffffffffu);
+                float bx, by, bqw, bqz, d0, d1; int type;
+                if (id & 0x4000u) {
+                    const int j = id & 0x3fff;
+                    const float4 o0 = sm.a0[j]; const float4 gb = sc.ag_b[j];
+                    bx = o0.x; by = o0.y; bqw = o0.z; bqz = o0.w; d0 = gb.x; d1 = gb.y; type = (int)gb.w;
+                } else {
+                    const float4 ra = sc.road_a[id]; const float2 rb = sc.road_b[id];
+                    bx = ra.x; by = ra.y; bqw = ra.z; bqz = ra.w; d0 = rb.x; d1 = rb.y; type = (int)(sc.road_c[id] >> 8);
+                }
+                const float2 d = wp.raydir[i % NRAY];
+                const float te = ray_box_exact(px, py, bx, by, bqw, bqz, d0, d1, d.x, d.y);
+                if (te >= 0.f) t = te;      // (a grazing ray may flip to a miss in exact arithmetic: keep the fast t)
+                const float2 xy = wp.rayxy[i % NRAY];
+                v = make_float4(t, (float)type, __fmul_rn(t, xy.x), __fmul_rn(t, xy.y));
+            }
+            out[i] = v;
+        }
+        __syncwarp();
+    }
+
+    // ------------------------------------------------------------ road-map rows
+    if (!classical) return;
+    const int K = kMaxAgentMapObs;
+    float *rows = ex.agent_roadmap + wa * K * kMapObsSize;
+    int32_t *kidx = ex.knn_idx + wa * K;
+    int emitted = 0;
+
+    // selection threshold: accept key < thr, plus the first need_eq entries with key == thr
+    unsigned thr = 0xffffffffu; int need_eq = 0;
+    const bool overflow = cnt > OBS_CAND;
+    const int C = min(cnt, OBS_CAND);
+    bool take_all = cnt <= K;
+    if (first_k_only) take_all = true;     // first K in index order (sim.cpp:261-279)
+
+    if (!take_all) {
+        // exact radix select (4 x 8 bits, MSB first) of the K-th smallest key among in-radius entities
+        unsigned prefix = 0; int remaining = K;
+        for (int pass = 0; pass < 4; pass++) {
+            const int shift = 24 - 8 * pass;
+            __syncwarp();
+            for (int i = lane; i < 256; i += 32) wp.q.hist[i] = 0;
+            __syncwarp();
+            const unsigned hi_mask = pass == 0 ? 0u : (0xffffffffu << (shift + 8));
+            if (!overflow) {
+                for (int i = lane; i < C; i += 32) {
+                    const unsigned kb = __float_as_uint(wp.ckey[i]);
+                    if ((kb & hi_mask) == prefix) atomicAdd(&wp.q.hist[(kb >> shift) & 255], 1u);
+                }
+            } else {   // candidate list overflowed: recompute keys from the pooled road table
+                for (int r = lane; r < R; r += 32) {
+                    const float4 ra = sc.road_a[r];
+                    float ox, oy;
+                    inv_rotate_xy(qw, qz, __fsub_rn(ra.x, px), __fsub_rn(ra.y, py), ox, oy);
+                    const float key = len2_xy(ox, oy);
+                    if (!(key <= key_thr)) continue;
+                    const unsigned kb = __float_as_uint(key);
+                    if ((kb & hi_mask) == prefix) atomicAdd(&wp.q.hist[(kb >> shift) & 255], 1u);
+                }
+            }
+            __syncwarp();
+            // locate the bin holding the remaining-th element: lane owns bins [8*lane, 8*lane+8)
+            unsigned local[8]; unsigned sum = 0;
+#pragma unroll
+            for (int k = 0; k < 8; k++) { local[k] = wp.q.hist[lane * 8 + k]; sum += local[k]; }
+            unsigned incl = sum;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                unsigned v = __shfl_up_sync(FULL, incl, o);
+                if (lane >= o) incl += v;
+            }
+            const unsigned excl = incl - sum;
+            const bool mine = (unsigned)remaining > excl && (unsigned)remaining <= incl;
+            int digit = 0; int before = 0;
+            if (mine) {
+                unsigned acc = excl;
+#pragma unroll
+                for (int k = 0; k < 8; k++) {
+                    if ((unsigned)remaining > acc && (unsigned)remaining <= acc + local[k]) { digit = lane * 8 + k; before = (int)acc; }
+                    acc += local[k];
+                }
+            }
+            const unsigned who = __ballot_sync(FULL, mine);
+            const int src = __ffs(who) - 1;
+            digit = __shfl_sync(FULL, digit, src);
+            before = __shfl_sync(FULL, before, src);
+            prefix |= (unsigned)digit << shift;
+            remaining -= before;
+        }
+        thr = prefix;
+        need_eq = remaining;       // entries equal to thr still to take, lowest road index first
+        __syncwarp();
+    }
+
+    // emission in road-index order
+    {
+        int eq_seen = 0;
+        const bool rescan = overflow && !take_all;
+        const int N = rescan ? R : C;
+        for (int base = 0; base < N && emitted < K; base += 32) {
+            const int i = base + lane;
+            bool acc = false; unsigned ridx = 0; unsigned kb = 0;
+            if (i < N) {
+                if (rescan) {
+                    const float4 ra = sc.road_a[i];
+                    float ox, oy;
+                    inv_rotate_xy(qw, qz, __fsub_rn(ra.x, px), __fsub_rn(ra.y, py), ox, oy);
+                    const float key = len2_xy(ox, oy);
+                    acc = key <= key_thr;
+                    kb = __float_as_uint(key); ridx = (unsigned)i;
+                } else {
+                    acc = true; kb = __float_as_uint(wp.ckey[i]); ridx = wp.cidx[i];
+                }
+            }
+            if (!take_all) {
+                const bool is_eq = acc && kb == thr;
+                const unsigned em = __ballot_sync(FULL, is_eq);
+                const int eq_rank = eq_seen + __popc(em & lt_mask);
+                acc = acc && (kb < thr || (is_eq && eq_rank < need_eq));
+                eq_seen += __popc(em);
+            }
+            const unsigned am = __ballot_sync(FULL, acc);
+            int rank = __popc(am & lt_mask);
+            int m = __popc(am);
+            if (emitted + m > K) { m = K - emitted; if (rank >= m) acc = false; }
+            float row[9];
+            if (acc) {
+                const float4 ra = sc.road_a[ridx]; const float2 rb = sc.road_b[ridx];
+                const float4 rd = sc.road_d[ridx]; const uint32_t rc = sc.road_c[ridx];
+                float ox, oy, rw, rz;
+                inv_rotate_xy(qw, qz, __fsub_rn(ra.x, px), __fsub_rn(ra.y, py), ox, oy);
+                inv_mul_quat(qw, qz, ra.z, ra.w, rw, rz);
+                row[0] = ox; row[1] = oy; row[2] = rb.x; row[3] = rb.y; row[4] = rd.x;
+                row[5] = quat_to_yaw(rw, rz); row[6] = (float)(rc >> 8); row[7] = rd.z; row[8] = rd.w;
+                if (write_knn_idx) kidx[emitted + rank] = (int32_t)ridx;
+            }
+            flush_rows(wp.u.stage, rows + (size_t)emitted * 9, row, acc, rank, m, lane);
+            emitted += m;
+        }
+    }
+    // padding rows: fillZeros (knn.hpp:19-28 -> id = 0, mapType = 0) for the k-nearest algorithm,
+    // MapObservation::zero() (id = -1, mapType = -1) for the linear one (sim.cpp:277-279)
+    {
+        const float padv = first_k_only ? -1.f : 0.f;
+        const int n = (K - emitted) * 9;
+        float *dst = rows + (size_t)emitted * 9;
+        for (int i = lane; i < n; i += 32) dst[i] = (i % 9) >= 7 ? padv : 0.f;
+        if (write_knn_idx)
+            for (int i = emitted + lane; i < K; i += 32) kidx[i] = -1;
+    }
+}
+
+} // namespace gd
