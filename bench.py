@@ -218,7 +218,9 @@ def main_engine(args):
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
 
-    W = (args.worlds or TOTAL_WORLDS) // world_size
+    from gpudrive_lab_b200 import shard
+    total_worlds = args.worlds or TOTAL_WORLDS
+    W = len(shard.world_block(total_worlds, rank, world_size))
     pd = params_dict()
     if rank == 0:
         scenes_u = make_scenes(UNIQUE_SCENES)
@@ -226,7 +228,7 @@ def main_engine(args):
         dist.barrier()
     scenes_u = make_scenes(UNIQUE_SCENES)
     # contiguous block of worlds per rank; world i uses scenario (global index) % UNIQUE_SCENES
-    scenes = [scenes_u[(rank * W + i) % UNIQUE_SCENES] for i in range(W)]
+    scenes = shard.scenes_for_rank(scenes_u, total_worlds, rank, world_size)
     t0 = time.time()
     sim = mg.SimManager(mg.madrona.ExecMode.CUDA, local_rank, scenes, engine_params(pd), max_agents=SLOTS)
     build_s = time.time() - t0
@@ -309,15 +311,9 @@ def main_engine(args):
     step_no[0] += e2e_steps
 
     # ---- reduce over ranks: max time, summed agent counts
-    vec = torch.tensor([ms_total, e2e_s, float(n_ctrl), float(n_live), kt["k_obs_ms"], kt["k_agents_ms"]],
-                       device="cuda", dtype=torch.float64)
-    if world_size > 1:
-        mx = vec.clone(); dist.all_reduce(mx, op=dist.ReduceOp.MAX)
-        sm = vec.clone(); dist.all_reduce(sm, op=dist.ReduceOp.SUM)
-        ms_total, e2e_s = float(mx[0]), float(mx[1])
-        tot_ctrl, tot_live = float(sm[2]), float(sm[3])
-    else:
-        tot_ctrl, tot_live = float(n_ctrl), float(n_live)
+    ms_total, (tot_ctrl, tot_live) = shard.reduce_timing(ms_total, [n_ctrl, n_live], device="cuda")
+    e2e_s, _ = shard.reduce_timing(e2e_s, [0.0], device="cuda")
+    episode_stats = shard.reduce_stats(sim.stats(), device="cuda")     # the one NCCL exchange of the job
 
     if rank == 0:
         value = tot_ctrl * args.steps / (ms_total * 1e-3)
@@ -335,8 +331,8 @@ def main_engine(args):
             "config": workload_config(world_size),
             "clocks": clocks,
             "e2e": {"value": e2e_value, "unit": "agent-steps/s", "steps": e2e_steps,
-                    "h2d_bytes_per_step": W * world_size * SLOTS * 3 * 4,
-                    "d2h_bytes_per_step": W * world_size * SLOTS * (4 + 4 + 20),
+                    "h2d_bytes_per_step": total_worlds * SLOTS * 3 * 4,
+                    "d2h_bytes_per_step": total_worlds * SLOTS * (4 + 4 + 20),
                     "api": "gd_step_host (pinned host actions in, reward/done/info out)"},
             "gpu_launches": launches,
             "roofline": {"bound": "hbm", "kernel": "k_obs", "achieved": achieved, "peak": peak, "unit": "GB/s",
@@ -346,6 +342,7 @@ def main_engine(args):
                          "step_bytes_per_agent_step": b_step,
                          "step_frac_of_hbm_roofline": (b_step * tot_live * args.steps / (ms_total * 1e-3) / 1e9) / (peak * world_size)},
             "agent_normalized_fps": tot_live * args.steps / (ms_total * 1e-3),
+            "episode_stats": episode_stats,
             "build_s": build_s,
         }
         if world_size == 1 and not args.no_cpu_baseline:

@@ -147,4 +147,17 @@ int gd_scene_tensors(const char *path, const GdParams *params, int32_t max_agent
     })
 }
 
+int gd_scene_road_pose(const char *path, const GdParams *params, int32_t max_agents, float *pose,
+                       int32_t rows_cap) {
+    GD_TRY({
+        gd::Params p = toParams(params);
+        gd::ParsedMap m = gd::parseMapFile(path, p.polylineReductionThreshold);
+        gd::SceneData s = gd::buildScene(m, p, max_agents, nullptr, 0);
+        for (int r = 0; r < s.numRoads && r < rows_cap; r++) {
+            float *row = pose + (size_t)r * 4;
+            row[0] = s.rz[r]; row[1] = s.rqw[r]; row[2] = s.rqz[r]; row[3] = 0.f;
+        }
+    })
+}
+
 } // extern "C"

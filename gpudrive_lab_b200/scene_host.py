@@ -32,5 +32,7 @@ def scene_tensors(path: str, params, max_agents: int = 128) -> dict:
     stat = np.zeros((max(A, 1), 16), np.float32)
     _capi.check(lib.gd_scene_tensors(str(path).encode(), C.byref(p), max_agents, map_obs.ctypes.data, R,
                                      traj.ctypes.data, stat.ctypes.data, A))
-    info.update(map_obs=map_obs[:R], traj=traj[:A], agent_static=stat[:A])
+    pose = np.zeros((max(R, 1), 4), np.float32)
+    _capi.check(lib.gd_scene_road_pose(str(path).encode(), C.byref(p), max_agents, pose.ctypes.data, R))
+    info.update(map_obs=map_obs[:R], traj=traj[:A], agent_static=stat[:A], road_pose=pose[:R])
     return info

@@ -152,6 +152,10 @@ int gd_scene_info(const char *scene_path, const GdParams *params, int32_t max_ag
 int gd_scene_tensors(const char *scene_path, const GdParams *params, int32_t max_agents,
                      float *map_obs, int32_t map_rows_cap, float *traj, float *agent_static,
                      int32_t agent_cap);
+/* Position.z and Rotation (w, z; x = y = 0) of every road entity: pose [num_roads,4] = {z, qw, qz, 0}
+ * (makeRoadEdge / makeCube / makeStopSign, src/level_gen.cpp:150-290). Host only. */
+int gd_scene_road_pose(const char *scene_path, const GdParams *params, int32_t max_agents, float *pose,
+                       int32_t rows_cap);
 
 #ifdef __cplusplus
 }
