@@ -163,8 +163,39 @@ int Engine::uploadScene(const SceneData &s, const std::string &key) {
         zcls[r] = (uint8_t)c;
     }
 
+    // spatial order for k_obs: by z-class, then Morton code of the (1 m quantised) position; classes are
+    // padded to whole groups of 32 so a group never mixes lidar planes
+    std::vector<int> sorted;       // sorted slot -> original road index, -1 = dummy
+    {
+        float minx = 3e38f, miny = 3e38f;
+        for (int r = 0; r < R; r++) { minx = std::min(minx, s.rx[r]); miny = std::min(miny, s.ry[r]); }
+        auto spread = [](uint32_t v) {
+            uint64_t x = v & 0xffffu;
+            x = (x | (x << 8)) & 0x00ff00ffull; x = (x | (x << 4)) & 0x0f0f0f0full;
+            x = (x | (x << 2)) & 0x33333333ull; x = (x | (x << 1)) & 0x55555555ull;
+            return x;
+        };
+        std::vector<std::pair<uint64_t, int>> keys(R);
+        for (int r = 0; r < R; r++) {
+            const uint32_t qx = (uint32_t)std::min(65535.f, std::max(0.f, s.rx[r] - minx));
+            const uint32_t qy = (uint32_t)std::min(65535.f, std::max(0.f, s.ry[r] - miny));
+            keys[r] = {((uint64_t)zcls[r] << 32) | spread(qx) | (spread(qy) << 1), r};
+        }
+        std::sort(keys.begin(), keys.end());
+        for (int i = 0; i < R; i++) {
+            if (i > 0 && (keys[i].first >> 32) != (keys[i - 1].first >> 32))
+                while (sorted.size() % 32) sorted.push_back(-1);
+            sorted.push_back(keys[i].second);
+        }
+        while (sorted.size() % 32) sorted.push_back(-1);
+    }
+    const int RS = (int)sorted.size(), G = RS / 32;
+
     size_t off = 0;
     auto section = [&](size_t bytes) { size_t o = off; off += (bytes + 15) & ~size_t(15); return o; };
+    const size_t o_sa = section(sizeof(float4) * RS), o_sb = section(sizeof(float2) * RS),
+                 o_sc = section(sizeof(uint32_t) * RS), o_sd = section(sizeof(float4) * RS),
+                 o_gr = section(sizeof(float4) * std::max(G, 1));
     const size_t o_ra = section(sizeof(float4) * Rpad), o_rb = section(sizeof(float2) * Rpad),
                  o_rc = section(sizeof(uint32_t) * Rpad), o_rd = section(sizeof(float4) * Rpad),
                  o_cc = section(sizeof(float4) * Cpad), o_co = section(sizeof(float4) * 4 * Cpad),
@@ -186,6 +217,43 @@ int Engine::uploadScene(const SceneData &s, const std::string &key) {
     for (int r = R; r < Rpad; r++) {   // padding far away, never in any radius
         ra[r] = make_float4(1e30f, 1e30f, 1.f, 0.f);
         rb[r] = make_float2(1.f, 1.f);
+    }
+    {
+        float4 *sa = F4(o_sa), *sd = F4(o_sd), *gr = F4(o_gr);
+        float2 *sb = reinterpret_cast<float2 *>(blob.data() + o_sb);
+        uint32_t *scc = reinterpret_cast<uint32_t *>(blob.data() + o_sc);
+        for (int i = 0; i < RS; i++) {
+            const int r = sorted[i];
+            if (r < 0) {     // dummy: never in a radius, never in lidar range, z-class 8 (no plane)
+                sa[i] = make_float4(1e30f, 1e30f, 1.f, 0.f); sb[i] = make_float2(1.f, 1.f);
+                scc[i] = 8u; sd[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+            } else {
+                sa[i] = ra[r]; sb[i] = rb[r]; sd[i] = rd[r];
+                scc[i] = rc[r] | ((uint32_t)r << 16);
+            }
+        }
+        for (int g = 0; g < G; g++) {
+            float lox = 3e38f, loy = 3e38f, hix = -3e38f, hiy = -3e38f;
+            uint32_t cmask = 0;
+            for (int k = 0; k < 32; k++) {
+                const int r = sorted[g * 32 + k];
+                if (r < 0) continue;
+                lox = std::min(lox, s.rx[r]); hix = std::max(hix, s.rx[r]);
+                loy = std::min(loy, s.ry[r]); hiy = std::max(hiy, s.ry[r]);
+                cmask |= 1u << zcls[r];
+            }
+            const float cx = 0.5f * (lox + hix), cy = 0.5f * (loy + hiy);
+            float rad = 0.f;
+            for (int k = 0; k < 32; k++) {
+                const int r = sorted[g * 32 + k];
+                if (r < 0) continue;
+                const float dx = s.rx[r] - cx, dy = s.ry[r] - cy;
+                rad = std::max(rad, sqrtf(dx * dx + dy * dy) + s.rd0[r] + s.rd1[r]);
+            }
+            float4 v = make_float4(cx, cy, rad * 1.0001f + 1e-3f, 0.f);
+            memcpy(&v.w, &cmask, 4);
+            gr[g] = v;
+        }
     }
     for (int i = 0; i < C; i++) {
         const int r = coll[i];
@@ -225,6 +293,12 @@ int Engine::uploadScene(const SceneData &s, const std::string &key) {
     dev.road_b = reinterpret_cast<const float2 *>(base + o_rb);
     dev.road_c = reinterpret_cast<const uint32_t *>(base + o_rc);
     dev.road_d = reinterpret_cast<const float4 *>(base + o_rd);
+    dev.s_a = reinterpret_cast<const float4 *>(base + o_sa);
+    dev.s_b = reinterpret_cast<const float2 *>(base + o_sb);
+    dev.s_c = reinterpret_cast<const uint32_t *>(base + o_sc);
+    dev.s_d = reinterpret_cast<const float4 *>(base + o_sd);
+    dev.grp = reinterpret_cast<const float4 *>(base + o_gr);
+    dev.numGroups = G;
     dev.coll_cull = reinterpret_cast<const float4 *>(base + o_cc);
     dev.coll_obb = reinterpret_cast<const float4 *>(base + o_co);
     dev.traj = reinterpret_cast<const float *>(base + o_tr);

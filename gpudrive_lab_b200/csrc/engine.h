@@ -23,6 +23,13 @@ struct SceneDev {
     const float2 *road_b;     // [Rpad] d0, d1
     const uint32_t *road_c;   // [Rpad] zclass | type << 8
     const float4 *road_d;     // [Rpad] d2, yaw(heading), id, mapType   (row emission only)
+    // The same road entities sorted by (z-class, Morton code of the position) and cut into groups of 32
+    // (each class padded to a multiple of 32 with far-away dummies), for the observation kernel:
+    const float4 *s_a;        // [G*32] x, y, qw, qz
+    const float2 *s_b;        // [G*32] d0, d1
+    const uint32_t *s_c;      // [G*32] zclass | type << 8 | original road index << 16   (dummy: zclass 8)
+    const float4 *s_d;        // [G*32] d2, yaw(heading), id, mapType
+    const float4 *grp;        // [G] bounding circle cx, cy, r (covers every member box) | z-class bit mask
     const float4 *coll_cull;  // [Cpad] cx, cy, bounding radius, type
     const float4 *coll_obb;   // [Cpad*4] corners(8) | axes(4) | origin(2) z dz
     const float *traj;        // [A][1456]
@@ -33,7 +40,7 @@ struct SceneDev {
     float zc_z[kMaxZClasses];   // distinct (z, d2) pairs of the road entities
     float zc_d2[kMaxZClasses];
     int32_t numZClasses;
-    int32_t numRoads, numAgents, numColl;
+    int32_t numRoads, numAgents, numColl, numGroups;
     float mean[3];
     int32_t mapName[32];
     int32_t scenarioId[32];

@@ -1,44 +1,50 @@
-// k_obs: observation fan-out of the step graph for one group of 16 agent slots of one world
-// (one warp per agent; the CTA shares a shared-memory tile of the world's road table).
+// k_obs: observation fan-out of the step graph, one warp per agent.
 //   collectSelfObsSystem / collectAbsoluteObservationsSystem   src/sim.cpp:168-186,769-783
 //   collectPartnerObsSystem                                     src/sim.cpp:188-240
 //   collectMapObservationsSystem + selectKNearestRoadEntities   src/sim.cpp:242-280, src/knn.hpp:103-158
 //   lidarSystem + BVH::traceRay + traceRayIntoConvexPolyhedron  src/sim.cpp:394-460,
 //                                   external/madrona/src/physics/broadphase.cpp:656-888
-// k-nearest: the heap of knn.hpp is replaced by in-radius compaction (index order) -> exact radix
-// select of the K smallest (key, index) -> rows emitted in road-index order. Keys are computed with
-// the reference's operation order, so the selected SET is bit-exact.
-// lidar: the BVH is replaced by (1) near boxes first (the in-radius set of the k-nearest scan),
-// (2) far boxes culled by the fan cone, by a conservative angular range and by the closest hit found
-// so far on the rays they could touch, (3) surviving (box, ray) pairs pushed through a per-warp
-// shared-memory work queue so all 32 lanes clip rays in lock step. The clip itself is the
-// reference's slab test of the +-x / +-y faces written in the box frame.
+//
+// Road entities arrive spatially sorted in groups of 32 with a bounding circle per group (SceneDev::grp),
+// a one-level stand-in for the reference's BVH that fits a warp: one lane tests one group, and a group
+// that survives is processed by all 32 lanes at once.
+//   k-nearest: groups whose circle reaches the observation radius -> exact squared-distance keys ->
+//     in-radius candidates -> exact radix select of the K smallest (key, road index). The keys use the
+//     reference's operation order, so the selected SET is bit-exact.
+//   lidar: groups are visited in bands of increasing distance. Before each band the rays that are still
+//     "open" (no hit closer than the band) are gathered into one bit mask per plane; a group, and then a
+//     box, is skipped with one AND if the rays its angular range covers are all closed. Surviving
+//     (box, ray) pairs go through a per-warp shared-memory queue so 32 lanes clip rays in lock step; the
+//     closest hit per ray is kept with a 64-bit shared atomicMin of (t, box). Winners are re-clipped with
+//     the reference's exact object-space arithmetic at the end.
 #pragma once
 #include "device_math.cuh"
 #include "engine.h"
 
 namespace gd {
 
-constexpr int OBS_WARPS = 16;             // agents per CTA
+constexpr int OBS_WARPS = 8;              // agents per CTA
 constexpr int OBS_BLOCK = OBS_WARPS * 32;
-constexpr int OBS_TILE = 2304;            // road entities per shared-memory tile
-constexpr int OBS_CAND = 512;             // in-radius candidates kept per agent before fallback
+constexpr int OBS_CAND = 512;             // in-radius candidates kept per agent before the slow path
+constexpr int OBS_GCAP = 352;             // group descriptors per pass (11 per lane)
 constexpr int NRAY = kNumLidarSamples;    // 50
 constexpr int QCAP = 256;                 // lidar work-queue capacity per warp (power of two)
+constexpr int NBAND = 7;                  // distance bands: [0,4) [4,8) [8,16) [16,32) [32,64) [64,128) [128,inf)
 constexpr unsigned long long LIDAR_NONE = 0xFFFFFFFFFFFFFFFFull;
+constexpr unsigned long long RAY_ALL = (1ull << NRAY) - 1ull;
 
 struct ObsWarpSmem {
-    float ckey[OBS_CAND];                     // candidate squared distance (reference key)
-    uint16_t cidx[OBS_CAND];                  // candidate road index, ascending
+    uint32_t ckey[OBS_CAND];                  // candidate key: squared-distance bits (k-nearest) or road index (linear)
+    uint16_t cpos[OBS_CAND];                  // candidate slot in the sorted road arrays
     union {
-        unsigned long long best[3 * NRAY];    // lidar: (t bits << 32) | box id (road index, or 0x4000 | agent slot)
+        unsigned long long best[3 * NRAY];    // lidar: (t bits << 32) | box id (sorted slot, or 0x4000 | agent slot)
         float stage[32 * 9];                  // row transpose buffer for coalesced stores
     } u;
     union {
         uint32_t queue[QCAP];                 // lidar (box, ray, planes) work items
         uint32_t hist[256];                   // radix-select histogram
     } q;
-    uint32_t inmask[OBS_TILE / 32];           // per 32-entity group: lanes whose entity is in radius
+    uint32_t glist[OBS_GCAP];                 // surviving groups: id | band << 12 | lo << 15 | hi << 21 | near << 27 | planes << 28
     float2 raydir[NRAY];                      // normalised world-space direction
     float2 rayxy[NRAY];                       // (cos theta, sin theta) in the agent frame
 };
@@ -46,9 +52,6 @@ struct ObsWarpSmem {
 struct ObsSmem {
     float4 a0[128];     // per agent slot: x, y, qw, qz
     float4 a1[128];     // z, speed, type, id
-    float4 ta[OBS_TILE];
-    float2 tb[OBS_TILE];
-    uint32_t tc[OBS_TILE];
     ObsWarpSmem wp[OBS_WARPS];
 };
 
@@ -60,16 +63,19 @@ struct LidarCtx {
     float ox, oy;        // ray origin (agent position)
     float fc, fs;        // cos / sin of the fan-frame x axis (middle of the fan) in world
     int head, tail;      // work-queue cursors (warp-uniform)
-    int tile_base;       // road index of the first entity of the tile in shared memory
 };
 
-// work item: [13:0] box index (tile-local road index or agent slot) | [14] agent | [20:15] ray | [23:21] planes
+// work item: [13:0] box (sorted road slot or agent slot) | [14] agent | [20:15] ray | [23:21] planes
 __device__ __forceinline__ uint32_t make_item(int box, bool agent, int ray, int pm) {
     return (uint32_t)box | (agent ? 0x4000u : 0u) | ((uint32_t)ray << 15) | ((uint32_t)pm << 21);
 }
 
 __device__ __forceinline__ float best_t(const unsigned long long *best, int plane, int ray) {
     return __uint_as_float((unsigned)(best[plane * NRAY + ray] >> 32));   // LIDAR_NONE reads as NaN
+}
+
+__device__ __forceinline__ unsigned long long ray_bits(int lo, int hi) {   // bits lo..hi, 0 <= lo <= hi < 64
+    return ((2ull << hi) - 1ull) & ~((1ull << lo) - 1ull);
 }
 
 // Clip one ray against one box in the box frame (pure rotation, unscaled): equivalent to
@@ -139,55 +145,42 @@ __device__ __forceinline__ float fast_atan2(float y, float x) {
     return y < 0.f ? -r : r;
 }
 
+// Ray index range [lo, hi] an angular interval (centre a, half width w, fan frame) can touch; false if none.
+__device__ __forceinline__ bool ray_range(float a, float w, int &lo, int &hi) {
+    const float inv_delta = (float)NRAY / (2.f * kLidarAngle);
+    const float half = 0.5f * (float)(NRAY - 1);
+    const float flo = (a - w) * inv_delta + half, fhi = (a + w) * inv_delta + half;
+    if (fhi < 0.f || flo > (float)(NRAY - 1)) return false;
+    lo = max(0, (int)ceilf(flo));
+    hi = min(NRAY - 1, (int)floorf(fhi));
+    return lo <= hi;
+}
+
 // Which rays can touch this box? Conservative: never drops a ray the exact clip would accept.
-// Returns a bit mask over [ilo, ilo + 63] of the rays that still need the clip, after dropping rays
-// whose current closest hit (on every plane the box belongs to) is nearer than the box can be.
-__device__ __forceinline__ unsigned long long lidar_consider(const LidarCtx &c, const unsigned long long *best,
-                                                             int pm, float bx, float by, float qw, float qz,
-                                                             float d0, float d1, int &ilo)
+// Returns false if none, else the ray index range [lo, hi].
+__device__ __forceinline__ bool lidar_consider(const LidarCtx &c, float bx, float by, float qw, float qz,
+                                               float d0, float d1, int &lo, int &hi)
 {
     const float relx = bx - c.ox, rely = by - c.oy;
     const float rbound = d0 + d1;                         // >= half diagonal
     const float D2 = relx * relx + rely * rely;
     const float range = kLidarDistance + rbound;
-    if (D2 > range * range) return 0ull;
+    if (!(D2 <= range * range)) return false;
     const float fx = c.fc * relx + c.fs * rely, fy = c.fc * rely - c.fs * relx;   // centre in the fan frame
-    const float delta = (2.f * kLidarAngle) / (float)NRAY;
-    const float half = 0.5f * (float)(NRAY - 1);
-    int lo = 0, hi = NRAY - 1;
+    lo = 0; hi = NRAY - 1;
     const float cphi = 1.f - 2.f * qz * qz, sphi = 2.f * qw * qz;
     const float e0x = d0 * cphi, e0y = d0 * sphi, e1x = -d1 * sphi, e1y = d1 * cphi;
     const float maxcross = fabsf(relx * e0y - rely * e0x) + fabsf(relx * e1y - rely * e1x);
     const float mindot = D2 - fabsf(relx * e0x + rely * e0y) - fabsf(relx * e1x + rely * e1y);
     const bool close_box = !(mindot > 1e-6f * D2) || D2 <= (rbound + 0.01f) * (rbound + 0.01f);
-    if (!close_box) {
-        const float cH = 0.5146014f, sH = 0.8574295f;     // cos / sin of 24.5 * delta + 4e-3 (fan half angle)
-        if (fx < -rbound) return 0ull;                    // behind the fan
-        if (cH * fy - sH * fx > rbound) return 0ull;      // beyond the last ray
-        if (cH * fy + sH * fx < -rbound) return 0ull;     // before the first ray
-        const float w = maxcross * __frcp_rn(mindot);     // tan of the half width; atan(w) <= w
-        if (w < 1.0f) {
-            const float wdt = w + 2e-3f;
-            const float a = fast_atan2(fy, fx);
-            const float flo = (a - wdt) / delta + half, fhi = (a + wdt) / delta + half;
-            if (fhi < 0.f || flo > (float)(NRAY - 1)) return 0ull;
-            lo = max(0, (int)ceilf(flo));
-            hi = min(NRAY - 1, (int)floorf(fhi));
-            if (lo > hi) return 0ull;
-        }
-    }
-    ilo = lo;
-    // closest possible hit on this box; rays already stopped nearer than that (on all its planes) are skipped
-    const float dmin = fmaxf(sqrtf(D2) - rbound, 0.f) * 0.9999f - 1e-4f;
-    unsigned long long m = 0ull;
-    for (int i = lo; i <= hi; i++) {
-        bool need = false;
-#pragma unroll
-        for (int p = 0; p < 3; p++)
-            if (pm & (1 << p)) need |= !(best_t(best, p, i) <= dmin);   // NaN (no hit yet) -> need
-        if (need) m |= 1ull << (i - lo);
-    }
-    return m;
+    if (close_box) return true;
+    const float cH = 0.5146014f, sH = 0.8574295f;     // cos / sin of 24.5 * delta + 4e-3 (fan half angle)
+    if (fx < -rbound) return false;                   // behind the fan
+    if (cH * fy - sH * fx > rbound) return false;     // beyond the last ray
+    if (cH * fy + sH * fx < -rbound) return false;    // before the first ray
+    const float w = maxcross * __frcp_rn(mindot);     // tan of the half width; atan(w) <= w
+    if (w < 1.0f) return ray_range(fast_atan2(fy, fx), w + 2e-3f, lo, hi);
+    return true;
 }
 
 // z-slab membership of the three lidar planes for a hull with object-space z in [zmin_obj, zmax_obj]
@@ -214,19 +207,19 @@ __device__ __forceinline__ void lidar_run_item(const ObsSmem &sm, const SceneDev
                                                const LidarCtx &c, uint32_t item)
 {
     const int box = item & 0x3fff, ray = (item >> 15) & 63, pm = (item >> 21) & 7;
-    float bx, by, qw, qz, d0, d1; unsigned id;
+    float bx, by, qw, qz, d0, d1;
     if (item & 0x4000u) {
         const float4 o0 = sm.a0[box]; const float4 gb = sc.ag_b[box];
-        bx = o0.x; by = o0.y; qw = o0.z; qz = o0.w; d0 = gb.x; d1 = gb.y; id = 0x4000u | (unsigned)box;
+        bx = o0.x; by = o0.y; qw = o0.z; qz = o0.w; d0 = gb.x; d1 = gb.y;
     } else {
-        const float4 ra = sm.ta[box]; const float2 rb = sm.tb[box];
-        bx = ra.x; by = ra.y; qw = ra.z; qz = ra.w; d0 = rb.x; d1 = rb.y; id = (unsigned)(c.tile_base + box);
+        const float4 ra = __ldg(&sc.s_a[box]); const float2 rb = __ldg(&sc.s_b[box]);
+        bx = ra.x; by = ra.y; qw = ra.z; qz = ra.w; d0 = rb.x; d1 = rb.y;
     }
     const float cphi = 1.f - 2.f * qz * qz, sphi = 2.f * qw * qz;
     const float2 d = wp.raydir[ray];
     const float t = ray_box(c.ox - bx, c.oy - by, cphi, sphi, d0, d1, d.x, d.y);
     if (t >= 0.f) {
-        const unsigned long long v = ((unsigned long long)__float_as_uint(t) << 32) | id;
+        const unsigned long long v = ((unsigned long long)__float_as_uint(t) << 32) | (item & 0x7fffu);
 #pragma unroll
         for (int p = 0; p < 3; p++)
             if (pm & (1 << p)) atomicMin(&wp.u.best[p * NRAY + ray], v);
@@ -244,9 +237,9 @@ __device__ __forceinline__ void lidar_drain(const ObsSmem &sm, const SceneDev &s
     }
 }
 
-// All 32 lanes call this together. `mask`: rays (relative to ilo) this lane's box still needs.
+// All 32 lanes call this together. `mask`: absolute ray bits this lane's box still needs.
 __device__ __forceinline__ void lidar_push(const ObsSmem &sm, const SceneDev &sc, ObsWarpSmem &wp, LidarCtx &c,
-                                           int lane, unsigned long long mask, int ilo, uint32_t base_item)
+                                           int lane, unsigned long long mask, uint32_t base_item)
 {
     const unsigned FULL = 0xffffffffu;
     const int n = __popcll(mask);
@@ -259,6 +252,19 @@ __device__ __forceinline__ void lidar_push(const ObsSmem &sm, const SceneDev &sc
     const int total = __shfl_sync(FULL, incl, 31);
     if (total == 0) return;
     const int off = incl - n;
+    if (total <= QCAP - (c.tail - c.head)) {       // common case: everything fits
+        int g = c.tail + off;
+        while (mask) {
+            const int b = __ffsll((long long)mask) - 1;
+            mask &= mask - 1;
+            wp.q.queue[g & (QCAP - 1)] = base_item | ((uint32_t)b << 15);
+            g++;
+        }
+        c.tail += total;
+        __syncwarp();
+        lidar_drain(sm, sc, wp, c, lane, false);
+        return;
+    }
     int base = 0;
     while (base < total) {
         const int space = QCAP - (c.tail - c.head);
@@ -269,7 +275,7 @@ __device__ __forceinline__ void lidar_push(const ObsSmem &sm, const SceneDev &sc
             const int b = __ffsll((long long)m) - 1;
             m &= m - 1;
             if (g >= base && g < base + take)
-                wp.q.queue[(c.tail + g - base) & (QCAP - 1)] = base_item | ((uint32_t)(ilo + b) << 15);
+                wp.q.queue[(c.tail + g - base) & (QCAP - 1)] = base_item | ((uint32_t)b << 15);
             g++;
         }
         c.tail += take;
@@ -277,6 +283,23 @@ __device__ __forceinline__ void lidar_push(const ObsSmem &sm, const SceneDev &sc
         __syncwarp();
         lidar_drain(sm, sc, wp, c, lane, false);
     }
+}
+
+// Rays of each plane with no hit closer than `dist` yet (bit i = ray i).
+__device__ __forceinline__ void open_rays(const unsigned long long *best, float dist, int lane,
+                                          unsigned long long (&open)[3])
+{
+    const unsigned FULL = 0xffffffffu;
+#pragma unroll
+    for (int p = 0; p < 3; p++) {
+        const bool a = !(best_t(best, p, lane) <= dist);                     // NaN (no hit) -> open
+        const bool b = lane + 32 < NRAY && !(best_t(best, p, min(lane + 32, NRAY - 1)) <= dist);
+        open[p] = (unsigned long long)__ballot_sync(FULL, a) | ((unsigned long long)__ballot_sync(FULL, b) << 32);
+    }
+}
+
+__device__ __forceinline__ unsigned long long open_for(const unsigned long long (&open)[3], int pm) {
+    return ((pm & 1) ? open[0] : 0ull) | ((pm & 2) ? open[1] : 0ull) | ((pm & 4) ? open[2] : 0ull);
 }
 
 // Emit `m` rows held one per lane (lanes with has_row) to consecutive global rows starting at dst,

@@ -6,7 +6,7 @@ namespace gd {
 
 // key_thr: largest float k with sqrtf(k) <= observationRadius, so `key <= key_thr` is exactly the
 // reference's `length() <= radius` (knn.hpp:88, sim.cpp:268-271) without a square root per entity.
-__global__ void __launch_bounds__(OBS_BLOCK, 1)
+__global__ void __launch_bounds__(OBS_BLOCK, 3)
 k_obs(const SceneDev *__restrict__ scenes, StateDev st, Exports ex, Params prm, int S, int groups,
       int write_knn_idx, float key_thr)
 {
@@ -34,7 +34,8 @@ k_obs(const SceneDev *__restrict__ scenes, StateDev st, Exports ex, Params prm, 
     __syncthreads();
 
     const int a = g * OBS_WARPS + warp;
-    const bool active = a < A;            // inactive warps still take part in the tile barriers
+    if (a >= A) return;                   // no block-wide barrier below this point
+    const bool active = true;
     ObsWarpSmem &wp = sm.wp[warp];
     const size_t wa = (size_t)w * S + (active ? a : 0);
 
@@ -100,9 +101,10 @@ k_obs(const SceneDev *__restrict__ scenes, StateDev st, Exports ex, Params prm, 
 
     // ------------------------------------------------------------ lidar set-up
     LidarCtx lc;
-    lc.ox = px; lc.oy = py; lc.fc = 1.f; lc.fs = 0.f; lc.head = 0; lc.tail = 0; lc.tile_base = 0;
-    int zmask_classes = 0;         // 3 bits per z-class
-    if (active && lidar_on) {
+    lc.ox = px; lc.oy = py; lc.fc = 1.f; lc.fs = 0.f; lc.head = 0; lc.tail = 0;
+    int zmask_classes = 0;         // 3 plane bits per z-class (bits >= 24 stay 0: dummy class 8 has no plane)
+    unsigned long long open[3] = {RAY_ALL, RAY_ALL, RAY_ALL};
+    if (lidar_on) {
         __syncwarp();
         for (int i = lane; i < 3 * NRAY; i += 32) wp.u.best[i] = LIDAR_NONE;
         const int controlled = ex.controlled[wa];
@@ -127,103 +129,128 @@ k_obs(const SceneDev *__restrict__ scenes, StateDev st, Exports ex, Params prm, 
         for (int c = 0; c < sc.numZClasses; c++)
             zmask_classes |= plane_mask(pz, sc.zc_z[c], sc.zc_d2[c], -1.f, 1.f) << (3 * c);
         __syncwarp();
-        // other agents first: few boxes, and their hits prune the road sweep on the edge plane
+        // other agents first: few boxes, and their hits close rays before the road groups are visited
         for (int base = 0; base < A; base += 32) {
             const int j = base + lane;
-            unsigned long long m = 0ull; int ilo = 0; int pm = 0;
+            unsigned long long m = 0ull; int pm = 0;
             if (j < A) {
                 const float4 o0 = sm.a0[j]; const float4 gb = sc.ag_b[j];
                 pm = plane_mask(pz, sm.a1[j].x, gb.z, 0.f, 2.f);
-                if (pm) m = lidar_consider(lc, wp.u.best, pm, o0.x, o0.y, o0.z, o0.w, gb.x, gb.y, ilo);
+                int lo, hi;
+                if (pm && lidar_consider(lc, o0.x, o0.y, o0.z, o0.w, gb.x, gb.y, lo, hi)) m = ray_bits(lo, hi);
             }
-            lidar_push(sm, sc, wp, lc, lane, m, ilo, make_item(j, true, 0, pm));
+            lidar_push(sm, sc, wp, lc, lane, m, make_item(j, true, 0, pm));
         }
-        lidar_drain(sm, sc, wp, lc, lane, true);
-    }
-
-    // ------------------------------------------------------------ road tiles: kNN candidates + lidar
-    int cnt = 0;                   // in-radius entities seen so far (warp-uniform)
-    const bool want_cands = active && classical;
-    const bool first_k_only = prm.roadObservationAlgorithm == RO_AllEntities;
-    const bool need_keys = want_cands || (active && lidar_on);
-    const float rpad = radius * 1.00001f + 1e-3f;      // |dx|,|dy| beyond this cannot be in radius
-    for (int t0 = 0; t0 < R; t0 += OBS_TILE) {
-        const int tl = min(OBS_TILE, R - t0);
-        __syncthreads();
-        for (int i = tid; i < tl; i += OBS_BLOCK) {
-            sm.ta[i] = sc.road_a[t0 + i];
-            sm.tb[i] = sc.road_b[t0 + i];
-            sm.tc[i] = sc.road_c[t0 + i];
-        }
-        __syncthreads();
-        if (!active || !need_keys) continue;
-        lc.tile_base = t0;
-        // ---- sweep 1: exact keys of nearby entities -> candidates; their boxes feed the lidar first
-        for (int base = 0; base < tl; base += 32) {
-            const int r = base + lane;
-            const bool valid = r < tl;
-            float4 ra = make_float4(0, 0, 1, 0);
-            bool nearb = false;
-            float dx = 0, dy = 0;
-            if (valid) {
-                ra = sm.ta[r];
-                dx = __fsub_rn(ra.x, px); dy = __fsub_rn(ra.y, py);
-                nearb = fabsf(dx) <= rpad && fabsf(dy) <= rpad;
-            }
-            unsigned inm = 0;
-            if (__any_sync(FULL, nearb)) {
-                bool in = false;
-                float key = 0.f;
-                if (nearb) {
-                    float ox, oy;
-                    inv_rotate_xy(qw, qz, dx, dy, ox, oy);
-                    key = len2_xy(ox, oy);
-                    in = key <= key_thr;
-                }
-                inm = __ballot_sync(FULL, in);
-                if (want_cands) {
-                    if (in) {
-                        const int pos = cnt + __popc(inm & lt_mask);
-                        if (pos < OBS_CAND) { wp.ckey[pos] = key; wp.cidx[pos] = (uint16_t)(t0 + r); }
-                    }
-                    cnt += __popc(inm);
-                }
-                if (lidar_on && inm) {
-                    unsigned long long m = 0ull; int ilo = 0; int pm = 0;
-                    if (in) {
-                        const uint32_t c = sm.tc[r];
-                        pm = (zmask_classes >> (3 * (c & 0xff))) & 7;
-                        if (pm) {
-                            const float2 rb = sm.tb[r];
-                            m = lidar_consider(lc, wp.u.best, pm, ra.x, ra.y, ra.z, ra.w, rb.x, rb.y, ilo);
-                        }
-                    }
-                    lidar_push(sm, sc, wp, lc, lane, m, ilo, make_item(r, false, 0, pm));
-                }
-            }
-            if (lidar_on && lane == 0) wp.inmask[base >> 5] = inm;
-        }
-        if (!lidar_on) continue;
         lidar_drain(sm, sc, wp, lc, lane, true);
         __syncwarp();
-        // ---- sweep 2: the far boxes, culled by cone / range / closest hit so far
-        for (int base = 0; base < tl; base += 32) {
-            const int r = base + lane;
-            const unsigned inm = wp.inmask[base >> 5];
-            unsigned long long m = 0ull; int ilo = 0; int pm = 0;
-            if (r < tl && !((inm >> lane) & 1u)) {
-                const uint32_t c = sm.tc[r];
-                pm = (zmask_classes >> (3 * (c & 0xff))) & 7;
-                if (pm) {
-                    const float4 ra = sm.ta[r]; const float2 rb = sm.tb[r];
-                    m = lidar_consider(lc, wp.u.best, pm, ra.x, ra.y, ra.z, ra.w, rb.x, rb.y, ilo);
+    }
+
+    // ------------------------------------------------------------ road groups: kNN candidates + lidar
+    int cnt = 0;                   // in-radius entities seen so far (warp-uniform)
+    const bool want_cands = classical;
+    const bool first_k_only = prm.roadObservationAlgorithm == RO_AllEntities;
+    const float rpad = radius * 1.00001f + 1e-3f;      // |dx|,|dy| beyond this cannot be in radius
+    const int G = sc.numGroups;
+    const int nZ = sc.numZClasses;
+    for (int g0 = 0; g0 < G && (want_cands || lidar_on); g0 += OBS_GCAP) {
+        // ---- one lane per group: can its bounding circle matter to this agent?
+        const int gN = min(OBS_GCAP, G - g0);
+        int nlist = 0;
+        __syncwarp();
+        for (int base = 0; base < gN; base += 32) {
+            const int gl = base + lane;
+            uint32_t desc = 0; bool keep = false;
+            if (gl < gN) {
+                const float4 gc = __ldg(&sc.grp[g0 + gl]);
+                const float relx = gc.x - px, rely = gc.y - py;
+                const float d = sqrtf(relx * relx + rely * rely);
+                const float dmin = fmaxf(d - gc.z, 0.f);
+                const bool nearg = want_cands && dmin <= rpad;
+                int pmg = 0, lo = 0, hi = NRAY - 1;
+                if (lidar_on && dmin <= kLidarDistance) {
+                    const unsigned cm = __float_as_uint(gc.w);
+                    for (int c = 0; c < nZ; c++)
+                        if ((cm >> c) & 1u) pmg |= (zmask_classes >> (3 * c)) & 7;
+                    if (pmg && d > gc.z * 1.0001f + 0.01f) {
+                        const float s = gc.z / d;                                   // sin of the half width
+                        const float w = s * rsqrtf(fmaxf(1.f - s * s, 1e-6f));      // tan >= the angle itself
+                        if (w < 3.f) {
+                            const float fx = lc.fc * relx + lc.fs * rely, fy = lc.fc * rely - lc.fs * relx;
+                            if (!ray_range(fast_atan2(fy, fx), w + 2e-3f, lo, hi)) pmg = 0;
+                        }
+                    }
+                }
+                keep = nearg || pmg != 0;
+                const int e = (int)(__float_as_uint(dmin) >> 23) - 127;           // floor(log2(dmin))
+                const int band = dmin < 4.f ? 0 : min(NBAND - 1, e - 1);
+                desc = (uint32_t)gl | ((uint32_t)band << 12) | ((uint32_t)lo << 15) | ((uint32_t)hi << 21) |
+                       (nearg ? (1u << 27) : 0u) | ((uint32_t)pmg << 28);
+            }
+            const unsigned km = __ballot_sync(FULL, keep);
+            if (keep) wp.glist[nlist + __popc(km & lt_mask)] = desc;
+            nlist += __popc(km);
+        }
+        __syncwarp();
+        // ---- bands of increasing distance
+        for (int band = 0; band < NBAND; band++) {
+            const float band_lo = band == 0 ? 0.f : (float)(2 << band);
+            if (lidar_on) open_rays(wp.u.best, band_lo * 0.9999f - 1e-3f, lane, open);
+            const bool any_open = lidar_on && (open[0] | open[1] | open[2]) != 0ull;
+            if (!any_open && !(want_cands && band_lo <= rpad)) break;     // nothing farther can matter
+            for (int base = 0; base < nlist; base += 32) {
+                const int li = base + lane;
+                const uint32_t desc = li < nlist ? wp.glist[li] : 0u;
+                const bool mine = li < nlist && (int)((desc >> 12) & 7u) == band;
+                const int pmg = (int)(desc >> 28);
+                const bool lid = mine && pmg != 0 &&
+                    (ray_bits((desc >> 15) & 63u, (desc >> 21) & 63u) & open_for(open, pmg)) != 0ull;
+                const bool nr = mine && ((desc >> 27) & 1u);
+                unsigned todo = __ballot_sync(FULL, lid || nr);
+                const unsigned lidm = __ballot_sync(FULL, lid), nrm = __ballot_sync(FULL, nr);
+                while (todo) {
+                    const int src = __ffs(todo) - 1;
+                    todo &= todo - 1;
+                    const int gid = g0 + (int)(__shfl_sync(FULL, desc, src) & 0xfffu);
+                    const bool do_l = (lidm >> src) & 1u, do_n = (nrm >> src) & 1u;
+                    const int e = gid * 32 + lane;
+                    const float4 ra = __ldg(&sc.s_a[e]);
+                    uint32_t c = 0;
+                    if (do_l || first_k_only) c = __ldg(&sc.s_c[e]);
+                    if (do_n) {
+                        const float dx = __fsub_rn(ra.x, px), dy = __fsub_rn(ra.y, py);
+                        bool in = false; float key = 0.f;
+                        if (fabsf(dx) <= rpad && fabsf(dy) <= rpad) {
+                            float ox, oy;
+                            inv_rotate_xy(qw, qz, dx, dy, ox, oy);
+                            key = len2_xy(ox, oy);
+                            in = key <= key_thr;
+                        }
+                        const unsigned inm = __ballot_sync(FULL, in);
+                        if (in) {
+                            const int pos = cnt + __popc(inm & lt_mask);
+                            if (pos < OBS_CAND) {
+                                wp.ckey[pos] = first_k_only ? (c >> 16) : __float_as_uint(key);
+                                wp.cpos[pos] = (uint16_t)e;
+                            }
+                        }
+                        cnt += __popc(inm);
+                    }
+                    if (do_l) {
+                        const int pm = (zmask_classes >> (3 * (int)(c & 0xffu))) & 7;
+                        unsigned long long m = 0ull;
+                        if (pm) {
+                            const float2 rb = __ldg(&sc.s_b[e]);
+                            int lo, hi;
+                            if (lidar_consider(lc, ra.x, ra.y, ra.z, ra.w, rb.x, rb.y, lo, hi))
+                                m = ray_bits(lo, hi) & open_for(open, pm);
+                        }
+                        lidar_push(sm, sc, wp, lc, lane, m, make_item(e, false, 0, pm));
+                    }
                 }
             }
-            lidar_push(sm, sc, wp, lc, lane, m, ilo, make_item(r, false, 0, pm));
+            if (lidar_on) { lidar_drain(sm, sc, wp, lc, lane, true); __syncwarp(); }
         }
-        lidar_drain(sm, sc, wp, lc, lane, true);   // items index this tile: finish before it is replaced
     }
-    if (!active) return;
 
     // ------------------------------------------------------------ lidar write-out
     if (lidar_on) {
@@ -241,8 +268,9 @@ k_obs(const SceneDev *__restrict__ scenes, StateDev st, Exports ex, Params prm, 
                     const float4 o0 = sm.a0[j]; const float4 gb = sc.ag_b[j];
                     bx = o0.x; by = o0.y; bqw = o0.z; bqz = o0.w; d0 = gb.x; d1 = gb.y; type = (int)gb.w;
                 } else {
-                    const float4 ra = sc.road_a[id]; const float2 rb = sc.road_b[id];
-                    bx = ra.x; by = ra.y; bqw = ra.z; bqz = ra.w; d0 = rb.x; d1 = rb.y; type = (int)(sc.road_c[id] >> 8);
+                    const float4 ra = __ldg(&sc.s_a[id]); const float2 rb = __ldg(&sc.s_b[id]);
+                    bx = ra.x; by = ra.y; bqw = ra.z; bqz = ra.w; d0 = rb.x; d1 = rb.y;
+                    type = (int)((__ldg(&sc.s_c[id]) >> 8) & 0xffu);
                 }
                 const float2 d = wp.raydir[i % NRAY];
                 const float te = ray_box_exact(px, py, bx, by, bqw, bqz, d0, d1, d.x, d.y);
@@ -261,38 +289,40 @@ k_obs(const SceneDev *__restrict__ scenes, StateDev st, Exports ex, Params prm, 
     float *rows = ex.agent_roadmap + wa * K * kMapObsSize;
     int32_t *kidx = ex.knn_idx + wa * K;
     int emitted = 0;
+    const int RS = G * 32;
 
-    // selection threshold: accept key < thr, plus the first need_eq entries with key == thr
-    unsigned thr = 0xffffffffu; int need_eq = 0;
+    // candidate key of sorted slot e (slow path only): in radius? and its selection key
+    auto slot_key = [&](int e, unsigned &kb) -> bool {
+        const float4 ra = __ldg(&sc.s_a[e]);
+        float ox, oy;
+        inv_rotate_xy(qw, qz, __fsub_rn(ra.x, px), __fsub_rn(ra.y, py), ox, oy);
+        const float key = len2_xy(ox, oy);
+        kb = first_k_only ? (__ldg(&sc.s_c[e]) >> 16) : __float_as_uint(key);
+        return key <= key_thr;
+    };
+
+    // selection: accept key < thr, plus the entries with key == thr whose road index is <= idx_thr.
+    // k-nearest: key = squared-distance bits, ties by road index (the heap of knn.hpp keeps the earlier
+    // index on equal distance); linear: key = road index, the first K in index order (sim.cpp:261-279).
+    unsigned thr = 0xffffffffu, idx_thr = 0xffffffffu;
     const bool overflow = cnt > OBS_CAND;
     const int C = min(cnt, OBS_CAND);
-    bool take_all = cnt <= K;
-    if (first_k_only) take_all = true;     // first K in index order (sim.cpp:261-279)
+    const bool take_all = cnt <= K;
+    const int N = overflow ? RS : C;
 
     if (!take_all) {
         // exact radix select (4 x 8 bits, MSB first) of the K-th smallest key among in-radius entities
-        unsigned prefix = 0; int remaining = K;
+        unsigned prefix = 0; int remaining = K; int count_eq = 0;
         for (int pass = 0; pass < 4; pass++) {
             const int shift = 24 - 8 * pass;
             __syncwarp();
             for (int i = lane; i < 256; i += 32) wp.q.hist[i] = 0;
             __syncwarp();
             const unsigned hi_mask = pass == 0 ? 0u : (0xffffffffu << (shift + 8));
-            if (!overflow) {
-                for (int i = lane; i < C; i += 32) {
-                    const unsigned kb = __float_as_uint(wp.ckey[i]);
-                    if ((kb & hi_mask) == prefix) atomicAdd(&wp.q.hist[(kb >> shift) & 255], 1u);
-                }
-            } else {   // candidate list overflowed: recompute keys from the pooled road table
-                for (int r = lane; r < R; r += 32) {
-                    const float4 ra = sc.road_a[r];
-                    float ox, oy;
-                    inv_rotate_xy(qw, qz, __fsub_rn(ra.x, px), __fsub_rn(ra.y, py), ox, oy);
-                    const float key = len2_xy(ox, oy);
-                    if (!(key <= key_thr)) continue;
-                    const unsigned kb = __float_as_uint(key);
-                    if ((kb & hi_mask) == prefix) atomicAdd(&wp.q.hist[(kb >> shift) & 255], 1u);
-                }
+            for (int i = lane; i < N; i += 32) {
+                unsigned kb; bool in = true;
+                if (overflow) in = slot_key(i, kb); else kb = wp.ckey[i];
+                if (in && (kb & hi_mask) == prefix) atomicAdd(&wp.q.hist[(kb >> shift) & 255], 1u);
             }
             __syncwarp();
             // locate the bin holding the remaining-th element: lane owns bins [8*lane, 8*lane+8)
@@ -307,12 +337,14 @@ k_obs(const SceneDev *__restrict__ scenes, StateDev st, Exports ex, Params prm, 
             }
             const unsigned excl = incl - sum;
             const bool mine = (unsigned)remaining > excl && (unsigned)remaining <= incl;
-            int digit = 0; int before = 0;
+            int digit = 0, before = 0, inbin = 0;
             if (mine) {
                 unsigned acc = excl;
 #pragma unroll
                 for (int k = 0; k < 8; k++) {
-                    if ((unsigned)remaining > acc && (unsigned)remaining <= acc + local[k]) { digit = lane * 8 + k; before = (int)acc; }
+                    if ((unsigned)remaining > acc && (unsigned)remaining <= acc + local[k]) {
+                        digit = lane * 8 + k; before = (int)acc; inbin = (int)local[k];
+                    }
                     acc += local[k];
                 }
             }
@@ -320,59 +352,61 @@ k_obs(const SceneDev *__restrict__ scenes, StateDev st, Exports ex, Params prm, 
             const int src = __ffs(who) - 1;
             digit = __shfl_sync(FULL, digit, src);
             before = __shfl_sync(FULL, before, src);
+            count_eq = __shfl_sync(FULL, inbin, src);
             prefix |= (unsigned)digit << shift;
             remaining -= before;
         }
         thr = prefix;
-        need_eq = remaining;       // entries equal to thr still to take, lowest road index first
         __syncwarp();
+        if (remaining < count_eq) {
+            // a true tie at the K-th key: take the `remaining` lowest road indices among the equal ones
+            unsigned last = 0; bool first = true;
+            for (int r = 0; r < remaining; r++) {
+                unsigned best_idx = 0xffffffffu;
+                for (int i = lane; i < N; i += 32) {
+                    unsigned kb; bool in = true; int e = i;
+                    if (overflow) in = slot_key(i, kb); else { kb = wp.ckey[i]; e = wp.cpos[i]; }
+                    if (in && kb == thr) {
+                        const unsigned oi = __ldg(&sc.s_c[e]) >> 16;
+                        if ((first || oi > last) && oi < best_idx) best_idx = oi;
+                    }
+                }
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) best_idx = min(best_idx, __shfl_xor_sync(FULL, best_idx, o));
+                last = best_idx; first = false;
+            }
+            idx_thr = last;
+        }
     }
 
-    // emission in road-index order
-    {
-        int eq_seen = 0;
-        const bool rescan = overflow && !take_all;
-        const int N = rescan ? R : C;
-        for (int base = 0; base < N && emitted < K; base += 32) {
-            const int i = base + lane;
-            bool acc = false; unsigned ridx = 0; unsigned kb = 0;
-            if (i < N) {
-                if (rescan) {
-                    const float4 ra = sc.road_a[i];
-                    float ox, oy;
-                    inv_rotate_xy(qw, qz, __fsub_rn(ra.x, px), __fsub_rn(ra.y, py), ox, oy);
-                    const float key = len2_xy(ox, oy);
-                    acc = key <= key_thr;
-                    kb = __float_as_uint(key); ridx = (unsigned)i;
-                } else {
-                    acc = true; kb = __float_as_uint(wp.ckey[i]); ridx = wp.cidx[i];
-                }
-            }
-            if (!take_all) {
-                const bool is_eq = acc && kb == thr;
-                const unsigned em = __ballot_sync(FULL, is_eq);
-                const int eq_rank = eq_seen + __popc(em & lt_mask);
-                acc = acc && (kb < thr || (is_eq && eq_rank < need_eq));
-                eq_seen += __popc(em);
-            }
-            const unsigned am = __ballot_sync(FULL, acc);
-            int rank = __popc(am & lt_mask);
-            int m = __popc(am);
-            if (emitted + m > K) { m = K - emitted; if (rank >= m) acc = false; }
-            float row[9];
-            if (acc) {
-                const float4 ra = sc.road_a[ridx]; const float2 rb = sc.road_b[ridx];
-                const float4 rd = sc.road_d[ridx]; const uint32_t rc = sc.road_c[ridx];
-                float ox, oy, rw, rz;
-                inv_rotate_xy(qw, qz, __fsub_rn(ra.x, px), __fsub_rn(ra.y, py), ox, oy);
-                inv_mul_quat(qw, qz, ra.z, ra.w, rw, rz);
-                row[0] = ox; row[1] = oy; row[2] = rb.x; row[3] = rb.y; row[4] = rd.x;
-                row[5] = quat_to_yaw(rw, rz); row[6] = (float)(rc >> 8); row[7] = rd.z; row[8] = rd.w;
-                if (write_knn_idx) kidx[emitted + rank] = (int32_t)ridx;
-            }
-            flush_rows(wp.u.stage, rows + (size_t)emitted * 9, row, acc, rank, m, lane);
-            emitted += m;
+    // emission (candidate order: by distance band, then by sorted slot)
+    for (int base = 0; base < N && emitted < K; base += 32) {
+        const int i = base + lane;
+        bool acc = false; int e = 0; unsigned kb = 0;
+        if (i < N) {
+            if (overflow) { e = i; acc = slot_key(i, kb); }
+            else { acc = true; kb = wp.ckey[i]; e = wp.cpos[i]; }
         }
+        uint32_t rc = 0;
+        if (acc) rc = __ldg(&sc.s_c[e]);
+        if (!take_all) acc = acc && (kb < thr || (kb == thr && (rc >> 16) <= idx_thr));
+        const unsigned am = __ballot_sync(FULL, acc);
+        int rank = __popc(am & lt_mask);
+        int m = __popc(am);
+        if (emitted + m > K) { m = K - emitted; if (rank >= m) acc = false; }
+        float row[9];
+        if (acc) {
+            const float4 ra = __ldg(&sc.s_a[e]); const float2 rb = __ldg(&sc.s_b[e]);
+            const float4 rd = __ldg(&sc.s_d[e]);
+            float ox, oy, rw, rz;
+            inv_rotate_xy(qw, qz, __fsub_rn(ra.x, px), __fsub_rn(ra.y, py), ox, oy);
+            inv_mul_quat(qw, qz, ra.z, ra.w, rw, rz);
+            row[0] = ox; row[1] = oy; row[2] = rb.x; row[3] = rb.y; row[4] = rd.x;
+            row[5] = quat_to_yaw(rw, rz); row[6] = (float)((rc >> 8) & 0xffu); row[7] = rd.z; row[8] = rd.w;
+            if (write_knn_idx) kidx[emitted + rank] = (int32_t)(rc >> 16);
+        }
+        flush_rows(wp.u.stage, rows + (size_t)emitted * 9, row, acc, rank, m, lane);
+        emitted += m;
     }
     // padding rows: fillZeros (knn.hpp:19-28 -> id = 0, mapType = 0) for the k-nearest algorithm,
     // MapObservation::zero() (id = -1, mapType = -1) for the linear one (sim.cpp:277-279)
