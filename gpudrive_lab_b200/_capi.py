@@ -5,7 +5,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libgpudrive_b200.so")
+LIB_PATH = os.environ.get("GD_B200_LIB") or os.path.join(_HERE, "libgpudrive_b200.so")   # override: kernel experiments
 
 
 class GdParams(C.Structure):

@@ -592,3 +592,12 @@ TensorDesc Engine::tensor(int id) const {
 }
 
 } // namespace gd
+
+#ifdef GD_COUNTERS
+extern "C" int gd_debug_counters(unsigned long long *out, int reset) {
+    cudaDeviceSynchronize();
+    cudaMemcpyFromSymbol(out, gd::g_obs_cnt, sizeof(unsigned long long) * 16);
+    if (reset) { unsigned long long z[16] = {0}; cudaMemcpyToSymbol(gd::g_obs_cnt, z, sizeof(z)); }
+    return 0;
+}
+#endif

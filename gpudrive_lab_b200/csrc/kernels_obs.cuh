@@ -23,27 +23,32 @@
 
 namespace gd {
 
+#ifdef GD_COUNTERS     // kernel experiments only: work counters read back through gd_debug_counters
+__device__ unsigned long long g_obs_cnt[16];
+#define GD_CNT(i, v) do { if (lane == 0) atomicAdd(&g_obs_cnt[i], (unsigned long long)(v)); } while (0)
+#else
+#define GD_CNT(i, v) do { } while (0)
+#endif
+
 constexpr int OBS_WARPS = 8;              // agents per CTA
 constexpr int OBS_BLOCK = OBS_WARPS * 32;
 constexpr int OBS_CAND = 512;             // in-radius candidates kept per agent before the slow path
-constexpr int OBS_GCAP = 352;             // group descriptors per pass (11 per lane)
+constexpr int OBS_GCAP = 128;             // group descriptors per pass (4 per lane; larger maps take several passes)
 constexpr int NRAY = kNumLidarSamples;    // 50
-constexpr int QCAP = 256;                 // lidar work-queue capacity per warp (power of two)
 constexpr int NBAND = 7;                  // distance bands: [0,4) [4,8) [8,16) [16,32) [32,64) [64,128) [128,inf)
-constexpr unsigned long long LIDAR_NONE = 0xFFFFFFFFFFFFFFFFull;
 constexpr unsigned long long RAY_ALL = (1ull << NRAY) - 1ull;
 
 struct ObsWarpSmem {
     uint32_t ckey[OBS_CAND];                  // candidate key: squared-distance bits (k-nearest) or road index (linear)
     uint16_t cpos[OBS_CAND];                  // candidate slot in the sorted road arrays
     union {
-        unsigned long long best[3 * NRAY];    // lidar: (t bits << 32) | box id (sorted slot, or 0x4000 | agent slot)
+        struct {
+            uint32_t bt[3 * NRAY];            // lidar: bits of the closest hit distance per plane and ray (none: ~0)
+            uint16_t bid[3 * NRAY];           // and its box: sorted road slot, or 0x4000 | agent slot
+        } l;
         float stage[32 * 9];                  // row transpose buffer for coalesced stores
     } u;
-    union {
-        uint32_t queue[QCAP];                 // lidar (box, ray, planes) work items
-        uint32_t hist[256];                   // radix-select histogram
-    } q;
+    uint32_t hist[256];                       // radix-select histogram
     uint32_t glist[OBS_GCAP];                 // surviving groups: id | band << 12 | lo << 15 | hi << 21 | near << 27 | planes << 28
     float2 raydir[NRAY];                      // normalised world-space direction
     float2 rayxy[NRAY];                       // (cos theta, sin theta) in the agent frame
@@ -62,20 +67,18 @@ struct ObsSmem {
 struct LidarCtx {
     float ox, oy;        // ray origin (agent position)
     float fc, fs;        // cos / sin of the fan-frame x axis (middle of the fan) in world
-    int head, tail;      // work-queue cursors (warp-uniform)
 };
 
-// work item: [13:0] box (sorted road slot or agent slot) | [14] agent | [20:15] ray | [23:21] planes
-__device__ __forceinline__ uint32_t make_item(int box, bool agent, int ray, int pm) {
-    return (uint32_t)box | (agent ? 0x4000u : 0u) | ((uint32_t)ray << 15) | ((uint32_t)pm << 21);
-}
-
-__device__ __forceinline__ float best_t(const unsigned long long *best, int plane, int ray) {
-    return __uint_as_float((unsigned)(best[plane * NRAY + ray] >> 32));   // LIDAR_NONE reads as NaN
+__device__ __forceinline__ float best_t(const uint32_t *bt, int plane, int ray) {
+    return __uint_as_float(bt[plane * NRAY + ray]);      // "none" (~0) reads as NaN
 }
 
 __device__ __forceinline__ unsigned long long ray_bits(int lo, int hi) {   // bits lo..hi, 0 <= lo <= hi < 64
     return ((2ull << hi) - 1ull) & ~((1ull << lo) - 1ull);
+}
+
+__device__ __forceinline__ unsigned long long open_for(const unsigned long long (&open)[3], int pm) {
+    return ((pm & 1) ? open[0] : 0ull) | ((pm & 2) ? open[1] : 0ull) | ((pm & 4) ? open[2] : 0ull);
 }
 
 // Clip one ray against one box in the box frame (pure rotation, unscaled): equivalent to
@@ -200,49 +203,18 @@ __device__ __forceinline__ int plane_mask(float pz, float bz, float d2, float zm
 }
 
 // ------------------------------------------------------------------------------------------
-// lidar work queue (per warp, shared memory ring): push (box, ray) items, clip 32 at a time
+// lidar clip stage: every lane brings one box and a ray range [lo, lo + n); the warp expands the 32
+// ranges into (box, ray) pairs, 32 pairs per round, one pair per lane. A lane finds its pair by a
+// binary search over the inclusive prefix sums and fetches the box from its owner with shuffles, so
+// no queue and no reload of the box are needed. The closest hit per (plane, ray) is kept as a native
+// 32-bit shared atomicMin on the bits of t; the box id is written by whichever lane holds the minimum
+// after the round's atomics (warp-synchronous, so the last writer is always the current minimum).
 // ------------------------------------------------------------------------------------------
-
-__device__ __forceinline__ void lidar_run_item(const ObsSmem &sm, const SceneDev &sc, ObsWarpSmem &wp,
-                                               const LidarCtx &c, uint32_t item)
-{
-    const int box = item & 0x3fff, ray = (item >> 15) & 63, pm = (item >> 21) & 7;
-    float bx, by, qw, qz, d0, d1;
-    if (item & 0x4000u) {
-        const float4 o0 = sm.a0[box]; const float4 gb = sc.ag_b[box];
-        bx = o0.x; by = o0.y; qw = o0.z; qz = o0.w; d0 = gb.x; d1 = gb.y;
-    } else {
-        const float4 ra = __ldg(&sc.s_a[box]); const float2 rb = __ldg(&sc.s_b[box]);
-        bx = ra.x; by = ra.y; qw = ra.z; qz = ra.w; d0 = rb.x; d1 = rb.y;
-    }
-    const float cphi = 1.f - 2.f * qz * qz, sphi = 2.f * qw * qz;
-    const float2 d = wp.raydir[ray];
-    const float t = ray_box(c.ox - bx, c.oy - by, cphi, sphi, d0, d1, d.x, d.y);
-    if (t >= 0.f) {
-        const unsigned long long v = ((unsigned long long)__float_as_uint(t) << 32) | (item & 0x7fffu);
-#pragma unroll
-        for (int p = 0; p < 3; p++)
-            if (pm & (1 << p)) atomicMin(&wp.u.best[p * NRAY + ray], v);
-    }
-}
-
-__device__ __forceinline__ void lidar_drain(const ObsSmem &sm, const SceneDev &sc, ObsWarpSmem &wp,
-                                            LidarCtx &c, int lane, bool final)
-{
-    while (c.tail - c.head >= 32 || (final && c.tail > c.head)) {
-        const int k = c.head + lane;
-        if (k < c.tail) lidar_run_item(sm, sc, wp, c, wp.q.queue[k & (QCAP - 1)]);
-        c.head = min(c.head + 32, c.tail);
-        __syncwarp();
-    }
-}
-
-// All 32 lanes call this together. `mask`: absolute ray bits this lane's box still needs.
-__device__ __forceinline__ void lidar_push(const ObsSmem &sm, const SceneDev &sc, ObsWarpSmem &wp, LidarCtx &c,
-                                           int lane, unsigned long long mask, uint32_t base_item)
+__device__ __forceinline__ void lidar_expand(ObsWarpSmem &wp, const LidarCtx &c, int lane, int lo, int n, int pm,
+                                             unsigned id, float bx, float by, float qw, float qz, float d0,
+                                             float d1, const unsigned long long (&open)[3])
 {
     const unsigned FULL = 0xffffffffu;
-    const int n = __popcll(mask);
     int incl = n;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
@@ -250,43 +222,51 @@ __device__ __forceinline__ void lidar_push(const ObsSmem &sm, const SceneDev &sc
         if (lane >= o) incl += v;
     }
     const int total = __shfl_sync(FULL, incl, 31);
+    GD_CNT(5, total); GD_CNT(6, 1);
     if (total == 0) return;
-    const int off = incl - n;
-    if (total <= QCAP - (c.tail - c.head)) {       // common case: everything fits
-        int g = c.tail + off;
-        while (mask) {
-            const int b = __ffsll((long long)mask) - 1;
-            mask &= mask - 1;
-            wp.q.queue[g & (QCAP - 1)] = base_item | ((uint32_t)b << 15);
-            g++;
+    const int excl = incl - n;
+    const float cphi = 1.f - 2.f * qz * qz, sphi = 2.f * qw * qz;
+    const unsigned meta = (unsigned)lo | ((unsigned)pm << 6) | (id << 9);
+    for (int base = 0; base < total; base += 32) {
+        const int j = base + lane;
+        int s = 0;                                   // owner: first lane whose inclusive sum exceeds j
+#pragma unroll
+        for (int step = 16; step > 0; step >>= 1) {
+            const int v = __shfl_sync(FULL, incl, s + step - 1);
+            if (v <= j) s += step;
         }
-        c.tail += total;
-        __syncwarp();
-        lidar_drain(sm, sc, wp, c, lane, false);
-        return;
-    }
-    int base = 0;
-    while (base < total) {
-        const int space = QCAP - (c.tail - c.head);
-        const int take = min(space, total - base);
-        unsigned long long m = mask;
-        int g = off;
-        while (m) {
-            const int b = __ffsll((long long)m) - 1;
-            m &= m - 1;
-            if (g >= base && g < base + take)
-                wp.q.queue[(c.tail + g - base) & (QCAP - 1)] = base_item | ((uint32_t)b << 15);
-            g++;
+        s = min(s, 31);
+        const float sbx = __shfl_sync(FULL, bx, s), sby = __shfl_sync(FULL, by, s);
+        const float sc_ = __shfl_sync(FULL, cphi, s), ss_ = __shfl_sync(FULL, sphi, s);
+        const float sd0 = __shfl_sync(FULL, d0, s), sd1 = __shfl_sync(FULL, d1, s);
+        const unsigned smeta = __shfl_sync(FULL, meta, s);
+        const int sexcl = __shfl_sync(FULL, excl, s);
+        const int ray = (int)(smeta & 63u) + (j - sexcl);
+        const int spm = (int)((smeta >> 6) & 7u);
+        unsigned tb = 0xffffffffu;
+        if (j < total && ((open_for(open, spm) >> ray) & 1ull)) {
+            const float2 d = wp.raydir[ray];
+            const float t = ray_box(c.ox - sbx, c.oy - sby, sc_, ss_, sd0, sd1, d.x, d.y);
+            if (t >= 0.f) {
+                tb = __float_as_uint(t);
+#pragma unroll
+                for (int p = 0; p < 3; p++)
+                    if (spm & (1 << p)) atomicMin(&wp.u.l.bt[p * NRAY + ray], tb);
+            }
         }
-        c.tail += take;
-        base += take;
+        GD_CNT(9, 1);
         __syncwarp();
-        lidar_drain(sm, sc, wp, c, lane, false);
+        if (tb != 0xffffffffu) {
+#pragma unroll
+            for (int p = 0; p < 3; p++)
+                if ((spm & (1 << p)) && wp.u.l.bt[p * NRAY + ray] == tb) wp.u.l.bid[p * NRAY + ray] = (uint16_t)(smeta >> 9);
+        }
     }
+    __syncwarp();
 }
 
 // Rays of each plane with no hit closer than `dist` yet (bit i = ray i).
-__device__ __forceinline__ void open_rays(const unsigned long long *best, float dist, int lane,
+__device__ __forceinline__ void open_rays(const uint32_t *best, float dist, int lane,
                                           unsigned long long (&open)[3])
 {
     const unsigned FULL = 0xffffffffu;
@@ -298,9 +278,6 @@ __device__ __forceinline__ void open_rays(const unsigned long long *best, float 
     }
 }
 
-__device__ __forceinline__ unsigned long long open_for(const unsigned long long (&open)[3], int pm) {
-    return ((pm & 1) ? open[0] : 0ull) | ((pm & 2) ? open[1] : 0ull) | ((pm & 4) ? open[2] : 0ull);
-}
 
 // Emit `m` rows held one per lane (lanes with has_row) to consecutive global rows starting at dst,
 // via the per-warp transpose buffer. rank = exclusive prefix of has_row.

@@ -4,9 +4,13 @@
 
 namespace gd {
 
+#ifndef GD_OBS_MINB
+#define GD_OBS_MINB 3
+#endif
+
 // key_thr: largest float k with sqrtf(k) <= observationRadius, so `key <= key_thr` is exactly the
 // reference's `length() <= radius` (knn.hpp:88, sim.cpp:268-271) without a square root per entity.
-__global__ void __launch_bounds__(OBS_BLOCK, 3)
+__global__ void __launch_bounds__(OBS_BLOCK, GD_OBS_MINB)
 k_obs(const SceneDev *__restrict__ scenes, StateDev st, Exports ex, Params prm, int S, int groups,
       int write_knn_idx, float key_thr)
 {
@@ -101,12 +105,12 @@ k_obs(const SceneDev *__restrict__ scenes, StateDev st, Exports ex, Params prm, 
 
     // ------------------------------------------------------------ lidar set-up
     LidarCtx lc;
-    lc.ox = px; lc.oy = py; lc.fc = 1.f; lc.fs = 0.f; lc.head = 0; lc.tail = 0;
+    lc.ox = px; lc.oy = py; lc.fc = 1.f; lc.fs = 0.f;
     int zmask_classes = 0;         // 3 plane bits per z-class (bits >= 24 stay 0: dummy class 8 has no plane)
     unsigned long long open[3] = {RAY_ALL, RAY_ALL, RAY_ALL};
     if (lidar_on) {
         __syncwarp();
-        for (int i = lane; i < 3 * NRAY; i += 32) wp.u.best[i] = LIDAR_NONE;
+        for (int i = lane; i < 3 * NRAY; i += 32) wp.u.l.bt[i] = 0xffffffffu;
         const int controlled = ex.controlled[wa];
         const float head = controlled ? ex.action[wa * kActionSize + 2] : 0.f;   // sim.cpp:409
         float rgx, rgy, fwx, fwy;
@@ -132,16 +136,16 @@ k_obs(const SceneDev *__restrict__ scenes, StateDev st, Exports ex, Params prm, 
         // other agents first: few boxes, and their hits close rays before the road groups are visited
         for (int base = 0; base < A; base += 32) {
             const int j = base + lane;
-            unsigned long long m = 0ull; int pm = 0;
+            int pm = 0, lo = 0, n = 0;
+            float4 o0 = make_float4(0.f, 0.f, 1.f, 0.f); float4 gb = make_float4(1.f, 1.f, 1.f, 0.f);
             if (j < A) {
-                const float4 o0 = sm.a0[j]; const float4 gb = sc.ag_b[j];
+                o0 = sm.a0[j]; gb = sc.ag_b[j];
                 pm = plane_mask(pz, sm.a1[j].x, gb.z, 0.f, 2.f);
-                int lo, hi;
-                if (pm && lidar_consider(lc, o0.x, o0.y, o0.z, o0.w, gb.x, gb.y, lo, hi)) m = ray_bits(lo, hi);
+                int hi;
+                if (pm && lidar_consider(lc, o0.x, o0.y, o0.z, o0.w, gb.x, gb.y, lo, hi)) n = hi - lo + 1;
             }
-            lidar_push(sm, sc, wp, lc, lane, m, make_item(j, true, 0, pm));
+            lidar_expand(wp, lc, lane, lo, n, pm, 0x4000u | (unsigned)j, o0.x, o0.y, o0.z, o0.w, gb.x, gb.y, open);
         }
-        lidar_drain(sm, sc, wp, lc, lane, true);
         __syncwarp();
     }
 
@@ -191,10 +195,12 @@ k_obs(const SceneDev *__restrict__ scenes, StateDev st, Exports ex, Params prm, 
             nlist += __popc(km);
         }
         __syncwarp();
+        GD_CNT(0, 1); GD_CNT(1, nlist);
         // ---- bands of increasing distance
         for (int band = 0; band < NBAND; band++) {
             const float band_lo = band == 0 ? 0.f : (float)(2 << band);
-            if (lidar_on) open_rays(wp.u.best, band_lo * 0.9999f - 1e-3f, lane, open);
+            // rays with no hit nearer than the band: only these can still be improved from here on
+            if (lidar_on) open_rays(wp.u.l.bt, band_lo * 0.9999f - 1e-3f, lane, open);
             const bool any_open = lidar_on && (open[0] | open[1] | open[2]) != 0ull;
             if (!any_open && !(want_cands && band_lo <= rpad)) break;     // nothing farther can matter
             for (int base = 0; base < nlist; base += 32) {
@@ -210,9 +216,12 @@ k_obs(const SceneDev *__restrict__ scenes, StateDev st, Exports ex, Params prm, 
                 while (todo) {
                     const int src = __ffs(todo) - 1;
                     todo &= todo - 1;
-                    const int gid = g0 + (int)(__shfl_sync(FULL, desc, src) & 0xfffu);
-                    const bool do_l = (lidm >> src) & 1u, do_n = (nrm >> src) & 1u;
+                    const uint32_t gdesc = __shfl_sync(FULL, desc, src);
+                    const int gid = g0 + (int)(gdesc & 0xfffu);
+                    const bool do_l = (lidm >> src) & 1u;
+                    const bool do_n = (nrm >> src) & 1u;
                     const int e = gid * 32 + lane;
+                    GD_CNT(2, 1); GD_CNT(3, do_l ? 1 : 0); GD_CNT(4, do_n ? 1 : 0);
                     const float4 ra = __ldg(&sc.s_a[e]);
                     uint32_t c = 0;
                     if (do_l || first_k_only) c = __ldg(&sc.s_c[e]);
@@ -237,31 +246,36 @@ k_obs(const SceneDev *__restrict__ scenes, StateDev st, Exports ex, Params prm, 
                     }
                     if (do_l) {
                         const int pm = (zmask_classes >> (3 * (int)(c & 0xffu))) & 7;
-                        unsigned long long m = 0ull;
+                        int lo = 0, n = 0;
+                        float2 rb = make_float2(1.f, 1.f);
                         if (pm) {
-                            const float2 rb = __ldg(&sc.s_b[e]);
-                            int lo, hi;
-                            if (lidar_consider(lc, ra.x, ra.y, ra.z, ra.w, rb.x, rb.y, lo, hi))
-                                m = ray_bits(lo, hi) & open_for(open, pm);
+                            rb = __ldg(&sc.s_b[e]);
+                            int hi;
+                            if (lidar_consider(lc, ra.x, ra.y, ra.z, ra.w, rb.x, rb.y, lo, hi)) {
+                                // trim the range to its first / last open ray (holes inside are skipped per ray)
+                                const unsigned long long m = ray_bits(lo, hi) & open_for(open, pm);
+                                if (m) { lo = __ffsll((long long)m) - 1; n = 64 - __clzll((long long)m) - lo; }
+                            }
                         }
-                        lidar_push(sm, sc, wp, lc, lane, m, make_item(e, false, 0, pm));
+                        lidar_expand(wp, lc, lane, lo, n, pm, (unsigned)e, ra.x, ra.y, ra.z, ra.w, rb.x, rb.y, open);
                     }
                 }
             }
-            if (lidar_on) { lidar_drain(sm, sc, wp, lc, lane, true); __syncwarp(); }
+            __syncwarp();
         }
     }
 
+    GD_CNT(8, cnt); GD_CNT(10, cnt > OBS_CAND ? 1 : 0);
     // ------------------------------------------------------------ lidar write-out
     if (lidar_on) {
         __syncwarp();
         float4 *out = reinterpret_cast<float4 *>(ex.lidar + wa * 3 * NRAY * kLidarRowSize);
         for (int i = lane; i < 3 * NRAY; i += 32) {
-            const unsigned long long b = wp.u.best[i];
+            const uint32_t tbits = wp.u.l.bt[i];
             float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (b != LIDAR_NONE) {
-                float t = __uint_as_float((unsigned)(b >> 32));
-                const unsigned id = (unsigned)(b & 0xffffffffu);
+            if (tbits != 0xffffffffu) {
+                float t = __uint_as_float(tbits);
+                const unsigned id = wp.u.l.bid[i];
                 float bx, by, bqw, bqz, d0, d1; int type;
                 if (id & 0x4000u) {
                     const int j = id & 0x3fff;
@@ -316,19 +330,19 @@ k_obs(const SceneDev *__restrict__ scenes, StateDev st, Exports ex, Params prm, 
         for (int pass = 0; pass < 4; pass++) {
             const int shift = 24 - 8 * pass;
             __syncwarp();
-            for (int i = lane; i < 256; i += 32) wp.q.hist[i] = 0;
+            for (int i = lane; i < 256; i += 32) wp.hist[i] = 0;
             __syncwarp();
             const unsigned hi_mask = pass == 0 ? 0u : (0xffffffffu << (shift + 8));
             for (int i = lane; i < N; i += 32) {
                 unsigned kb; bool in = true;
                 if (overflow) in = slot_key(i, kb); else kb = wp.ckey[i];
-                if (in && (kb & hi_mask) == prefix) atomicAdd(&wp.q.hist[(kb >> shift) & 255], 1u);
+                if (in && (kb & hi_mask) == prefix) atomicAdd(&wp.hist[(kb >> shift) & 255], 1u);
             }
             __syncwarp();
             // locate the bin holding the remaining-th element: lane owns bins [8*lane, 8*lane+8)
             unsigned local[8]; unsigned sum = 0;
 #pragma unroll
-            for (int k = 0; k < 8; k++) { local[k] = wp.q.hist[lane * 8 + k]; sum += local[k]; }
+            for (int k = 0; k < 8; k++) { local[k] = wp.hist[lane * 8 + k]; sum += local[k]; }
             unsigned incl = sum;
 #pragma unroll
             for (int o = 1; o < 32; o <<= 1) {
