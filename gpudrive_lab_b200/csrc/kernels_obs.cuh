@@ -48,10 +48,14 @@ struct ObsWarpSmem {
         } l;
         float stage[32 * 9];                  // row transpose buffer for coalesced stores
     } u;
-    uint32_t hist[256];                       // radix-select histogram
-    uint32_t glist[OBS_GCAP];                 // surviving groups: id | band << 12 | lo << 15 | hi << 21 | near << 27 | planes << 28
-    float2 raydir[NRAY];                      // normalised world-space direction
-    float2 rayxy[NRAY];                       // (cos theta, sin theta) in the agent frame
+    union {                                   // the histogram is only needed after the lidar is written out
+        struct {
+            uint32_t glist[OBS_GCAP];         // surviving groups: id | band << 12 | lo << 15 | hi << 21 | near << 27 | planes << 28
+            float2 raydir[NRAY];              // normalised world-space direction
+            float2 rayxy[NRAY];               // (cos theta, sin theta) in the agent frame
+        } g;
+        uint32_t hist[256];                   // radix-select histogram
+    } v;
 };
 
 struct ObsSmem {
@@ -81,22 +85,30 @@ __device__ __forceinline__ unsigned long long open_for(const unsigned long long 
     return ((pm & 1) ? open[0] : 0ull) | ((pm & 2) ? open[1] : 0ull) | ((pm & 4) ? open[2] : 0ull);
 }
 
+// Approximate reciprocal (MUFU.RCP). Only on culling / candidate paths: everything exported is recomputed
+// with IEEE operations in the reference's order.
+__device__ __forceinline__ float rcp_fast(float x) {
+    float r;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+}
+
 // Clip one ray against one box in the box frame (pure rotation, unscaled): equivalent to
 // traceRayIntoConvexPolyhedron over the four vertical faces (broadphase.cpp:754-855) with
 // tfirst = 0, tlast = lidarDistance, "entering t >= tfirst" and "only back faces -> miss".
-__device__ __forceinline__ float ray_box(float rx, float ry, float cphi, float sphi, float d0, float d1,
+// (px, py): ray origin in the box frame. Explicit fmaf: this translation unit is compiled with --fmad=false.
+__device__ __forceinline__ float ray_box(float px, float py, float cphi, float sphi, float d0, float d1,
                                          float dx, float dy)
 {
-    const float px = cphi * rx + sphi * ry, py = cphi * ry - sphi * rx;     // origin in box frame
-    const float lx = cphi * dx + sphi * dy, ly = cphi * dy - sphi * dx;     // direction in box frame
+    const float lx = fmaf(cphi, dx, sphi * dy), ly = fmaf(cphi, dy, -(sphi * dx));   // direction in box frame
     float tnear = -1.f, tfar = kLidarDistance;
     if (lx != 0.f) {
-        const float inv = __frcp_rn(lx);
+        const float inv = rcp_fast(lx);
         const float t1 = (-d0 - px) * inv, t2 = (d0 - px) * inv;
         tnear = fminf(t1, t2); tfar = fminf(tfar, fmaxf(t1, t2));
     } else if (fabsf(px) > d0) return -1.f;
     if (ly != 0.f) {
-        const float inv = __frcp_rn(ly);
+        const float inv = rcp_fast(ly);
         const float t1 = (-d1 - py) * inv, t2 = (d1 - py) * inv;
         tnear = fmaxf(tnear, fminf(t1, t2)); tfar = fminf(tfar, fmaxf(t1, t2));
     } else if (fabsf(py) > d1) return -1.f;
@@ -140,9 +152,9 @@ __device__ __forceinline__ float ray_box_exact(float ox, float oy, float bx, flo
 __device__ __forceinline__ float fast_atan2(float y, float x) {
     const float ax = fabsf(x), ay = fabsf(y);
     const float mx = fmaxf(ax, ay), mn = fminf(ax, ay);
-    const float a = mn * __frcp_rn(fmaxf(mx, 1e-30f));
+    const float a = mn * rcp_fast(fmaxf(mx, 1e-30f));
     const float s = a * a;
-    float r = ((-0.0464964749f * s + 0.15931422f) * s - 0.327622764f) * s * a + a;
+    float r = fmaf(fmaf(fmaf(-0.0464964749f, s, 0.15931422f), s, -0.327622764f) * s, a, a);
     if (ay > ax) r = 1.57079637f - r;
     if (x < 0.f) r = 3.14159274f - r;
     return y < 0.f ? -r : r;
@@ -152,7 +164,7 @@ __device__ __forceinline__ float fast_atan2(float y, float x) {
 __device__ __forceinline__ bool ray_range(float a, float w, int &lo, int &hi) {
     const float inv_delta = (float)NRAY / (2.f * kLidarAngle);
     const float half = 0.5f * (float)(NRAY - 1);
-    const float flo = (a - w) * inv_delta + half, fhi = (a + w) * inv_delta + half;
+    const float flo = fmaf(a - w, inv_delta, half), fhi = fmaf(a + w, inv_delta, half);
     if (fhi < 0.f || flo > (float)(NRAY - 1)) return false;
     lo = max(0, (int)ceilf(flo));
     hi = min(NRAY - 1, (int)floorf(fhi));
@@ -160,29 +172,29 @@ __device__ __forceinline__ bool ray_range(float a, float w, int &lo, int &hi) {
 }
 
 // Which rays can touch this box? Conservative: never drops a ray the exact clip would accept.
-// Returns false if none, else the ray index range [lo, hi].
-__device__ __forceinline__ bool lidar_consider(const LidarCtx &c, float bx, float by, float qw, float qz,
+// Returns false if none, else the ray index range [lo, hi]. (relx, rely): box centre relative to the ray
+// origin; (cphi, sphi): box axis.
+__device__ __forceinline__ bool lidar_consider(const LidarCtx &c, float relx, float rely, float cphi, float sphi,
                                                float d0, float d1, int &lo, int &hi)
 {
-    const float relx = bx - c.ox, rely = by - c.oy;
     const float rbound = d0 + d1;                         // >= half diagonal
-    const float D2 = relx * relx + rely * rely;
+    const float D2 = fmaf(relx, relx, rely * rely);
     const float range = kLidarDistance + rbound;
     if (!(D2 <= range * range)) return false;
-    const float fx = c.fc * relx + c.fs * rely, fy = c.fc * rely - c.fs * relx;   // centre in the fan frame
+    const float fx = fmaf(c.fc, relx, c.fs * rely), fy = fmaf(c.fc, rely, -(c.fs * relx));   // centre in the fan frame
     lo = 0; hi = NRAY - 1;
-    const float cphi = 1.f - 2.f * qz * qz, sphi = 2.f * qw * qz;
-    const float e0x = d0 * cphi, e0y = d0 * sphi, e1x = -d1 * sphi, e1y = d1 * cphi;
-    const float maxcross = fabsf(relx * e0y - rely * e0x) + fabsf(relx * e1y - rely * e1x);
-    const float mindot = D2 - fabsf(relx * e0x + rely * e0y) - fabsf(relx * e1x + rely * e1y);
+    // box half axes e0 = d0 (cphi, sphi), e1 = d1 (-sphi, cphi)
+    const float along = fmaf(relx, cphi, rely * sphi), across = fmaf(rely, cphi, -(relx * sphi));
+    const float maxcross = fmaf(d0, fabsf(across), d1 * fabsf(along));
+    const float mindot = D2 - fmaf(d0, fabsf(along), d1 * fabsf(across));
     const bool close_box = !(mindot > 1e-6f * D2) || D2 <= (rbound + 0.01f) * (rbound + 0.01f);
     if (close_box) return true;
     const float cH = 0.5146014f, sH = 0.8574295f;     // cos / sin of 24.5 * delta + 4e-3 (fan half angle)
     if (fx < -rbound) return false;                   // behind the fan
-    if (cH * fy - sH * fx > rbound) return false;     // beyond the last ray
-    if (cH * fy + sH * fx < -rbound) return false;    // before the first ray
-    const float w = maxcross * __frcp_rn(mindot);     // tan of the half width; atan(w) <= w
-    if (w < 1.0f) return ray_range(fast_atan2(fy, fx), w + 2e-3f, lo, hi);
+    if (fmaf(cH, fy, -(sH * fx)) > rbound) return false;     // beyond the last ray
+    if (fmaf(cH, fy, sH * fx) < -rbound) return false;       // before the first ray
+    const float w = maxcross * rcp_fast(mindot);      // tan of the half width; atan(w) <= w
+    if (w < 1.0f) return ray_range(fast_atan2(fy, fx), w * 1.0001f + 2e-3f, lo, hi);
     return true;
 }
 
@@ -210,9 +222,8 @@ __device__ __forceinline__ int plane_mask(float pz, float bz, float d2, float zm
 // 32-bit shared atomicMin on the bits of t; the box id is written by whichever lane holds the minimum
 // after the round's atomics (warp-synchronous, so the last writer is always the current minimum).
 // ------------------------------------------------------------------------------------------
-__device__ __forceinline__ void lidar_expand(ObsWarpSmem &wp, const LidarCtx &c, int lane, int lo, int n, int pm,
-                                             unsigned id, float bx, float by, float qw, float qz, float d0,
-                                             float d1, const unsigned long long (&open)[3])
+__device__ __forceinline__ void lidar_expand(ObsWarpSmem &wp, int lane, int lo, int n, int pm, unsigned id,
+                                             float relx, float rely, float cphi, float sphi, float d0, float d1)
 {
     const unsigned FULL = 0xffffffffu;
     int incl = n;
@@ -225,8 +236,9 @@ __device__ __forceinline__ void lidar_expand(ObsWarpSmem &wp, const LidarCtx &c,
     GD_CNT(5, total); GD_CNT(6, 1);
     if (total == 0) return;
     const int excl = incl - n;
-    const float cphi = 1.f - 2.f * qz * qz, sphi = 2.f * qw * qz;
-    const unsigned meta = (unsigned)lo | ((unsigned)pm << 6) | (id << 9);
+    // ray origin in the box frame (the box centre is (relx, rely) away from the origin)
+    const float opx = -fmaf(cphi, relx, sphi * rely), opy = -fmaf(cphi, rely, -(sphi * relx));
+    const unsigned meta = (unsigned)(lo - excl + 2048) | ((unsigned)pm << 12) | (id << 15);   // lo - excl in [-1600, 49]
     for (int base = 0; base < total; base += 32) {
         const int j = base + lane;
         int s = 0;                                   // owner: first lane whose inclusive sum exceeds j
@@ -235,31 +247,28 @@ __device__ __forceinline__ void lidar_expand(ObsWarpSmem &wp, const LidarCtx &c,
             const int v = __shfl_sync(FULL, incl, s + step - 1);
             if (v <= j) s += step;
         }
-        s = min(s, 31);
-        const float sbx = __shfl_sync(FULL, bx, s), sby = __shfl_sync(FULL, by, s);
+        const float spx = __shfl_sync(FULL, opx, s), spy = __shfl_sync(FULL, opy, s);
         const float sc_ = __shfl_sync(FULL, cphi, s), ss_ = __shfl_sync(FULL, sphi, s);
         const float sd0 = __shfl_sync(FULL, d0, s), sd1 = __shfl_sync(FULL, d1, s);
         const unsigned smeta = __shfl_sync(FULL, meta, s);
-        const int sexcl = __shfl_sync(FULL, excl, s);
-        const int ray = (int)(smeta & 63u) + (j - sexcl);
-        const int spm = (int)((smeta >> 6) & 7u);
+        const int ray = (int)(smeta & 4095u) - 2048 + j;
+        int spm = (int)((smeta >> 12) & 7u);
         unsigned tb = 0xffffffffu;
-        if (j < total && ((open_for(open, spm) >> ray) & 1ull)) {
-            const float2 d = wp.raydir[ray];
-            const float t = ray_box(c.ox - sbx, c.oy - sby, sc_, ss_, sd0, sd1, d.x, d.y);
+        if (j < total) {
+            const float2 d = wp.v.g.raydir[ray];
+            const float t = ray_box(spx, spy, sc_, ss_, sd0, sd1, d.x, d.y);
             if (t >= 0.f) {
                 tb = __float_as_uint(t);
-#pragma unroll
-                for (int p = 0; p < 3; p++)
-                    if (spm & (1 << p)) atomicMin(&wp.u.l.bt[p * NRAY + ray], tb);
+                for (int q = spm; q; q &= q - 1) atomicMin(&wp.u.l.bt[(__ffs(q) - 1) * NRAY + ray], tb);
             }
         }
         GD_CNT(9, 1);
         __syncwarp();
         if (tb != 0xffffffffu) {
-#pragma unroll
-            for (int p = 0; p < 3; p++)
-                if ((spm & (1 << p)) && wp.u.l.bt[p * NRAY + ray] == tb) wp.u.l.bid[p * NRAY + ray] = (uint16_t)(smeta >> 9);
+            for (; spm; spm &= spm - 1) {
+                const int k = (__ffs(spm) - 1) * NRAY + ray;
+                if (wp.u.l.bt[k] == tb) wp.u.l.bid[k] = (uint16_t)(smeta >> 15);
+            }
         }
     }
     __syncwarp();

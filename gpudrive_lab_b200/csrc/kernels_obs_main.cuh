@@ -5,7 +5,7 @@
 namespace gd {
 
 #ifndef GD_OBS_MINB
-#define GD_OBS_MINB 3
+#define GD_OBS_MINB 4
 #endif
 
 // key_thr: largest float k with sqrtf(k) <= observationRadius, so `key <= key_thr` is exactly the
@@ -123,8 +123,8 @@ k_obs(const SceneDev *__restrict__ scenes, StateDev st, Exports ex, Params prm, 
             const float dx = __fadd_rn(__fmul_rn(x, rgx), __fmul_rn(y, fwx));
             const float dy = __fadd_rn(__fmul_rn(x, rgy), __fmul_rn(y, fwy));
             const float inv = __fdiv_rn(1.f, __fsqrt_rn(__fadd_rn(len2_xy(dx, dy), 0.f)));
-            wp.raydir[i] = make_float2(__fmul_rn(dx, inv), __fmul_rn(dy, inv));
-            wp.rayxy[i] = make_float2(x, y);
+            wp.v.g.raydir[i] = make_float2(__fmul_rn(dx, inv), __fmul_rn(dy, inv));
+            wp.v.g.rayxy[i] = make_float2(x, y);
         }
         const float yaw = quat_to_yaw(qw, qz);
         const float delta = (2.f * kLidarAngle) / (float)NRAY;
@@ -137,14 +137,16 @@ k_obs(const SceneDev *__restrict__ scenes, StateDev st, Exports ex, Params prm, 
         for (int base = 0; base < A; base += 32) {
             const int j = base + lane;
             int pm = 0, lo = 0, n = 0;
-            float4 o0 = make_float4(0.f, 0.f, 1.f, 0.f); float4 gb = make_float4(1.f, 1.f, 1.f, 0.f);
+            float relx = 0.f, rely = 0.f, cphi = 1.f, sphi = 0.f, d0 = 1.f, d1 = 1.f;
             if (j < A) {
-                o0 = sm.a0[j]; gb = sc.ag_b[j];
+                const float4 o0 = sm.a0[j]; const float4 gb = sc.ag_b[j];
                 pm = plane_mask(pz, sm.a1[j].x, gb.z, 0.f, 2.f);
+                relx = o0.x - px; rely = o0.y - py; d0 = gb.x; d1 = gb.y;
+                cphi = 1.f - 2.f * o0.w * o0.w; sphi = 2.f * o0.z * o0.w;
                 int hi;
-                if (pm && lidar_consider(lc, o0.x, o0.y, o0.z, o0.w, gb.x, gb.y, lo, hi)) n = hi - lo + 1;
+                if (pm && lidar_consider(lc, relx, rely, cphi, sphi, d0, d1, lo, hi)) n = hi - lo + 1;
             }
-            lidar_expand(wp, lc, lane, lo, n, pm, 0x4000u | (unsigned)j, o0.x, o0.y, o0.z, o0.w, gb.x, gb.y, open);
+            lidar_expand(wp, lane, lo, n, pm, 0x4000u | (unsigned)j, relx, rely, cphi, sphi, d0, d1);
         }
         __syncwarp();
     }
@@ -191,7 +193,7 @@ k_obs(const SceneDev *__restrict__ scenes, StateDev st, Exports ex, Params prm, 
                        (nearg ? (1u << 27) : 0u) | ((uint32_t)pmg << 28);
             }
             const unsigned km = __ballot_sync(FULL, keep);
-            if (keep) wp.glist[nlist + __popc(km & lt_mask)] = desc;
+            if (keep) wp.v.g.glist[nlist + __popc(km & lt_mask)] = desc;
             nlist += __popc(km);
         }
         __syncwarp();
@@ -205,7 +207,7 @@ k_obs(const SceneDev *__restrict__ scenes, StateDev st, Exports ex, Params prm, 
             if (!any_open && !(want_cands && band_lo <= rpad)) break;     // nothing farther can matter
             for (int base = 0; base < nlist; base += 32) {
                 const int li = base + lane;
-                const uint32_t desc = li < nlist ? wp.glist[li] : 0u;
+                const uint32_t desc = li < nlist ? wp.v.g.glist[li] : 0u;
                 const bool mine = li < nlist && (int)((desc >> 12) & 7u) == band;
                 const int pmg = (int)(desc >> 28);
                 const bool lid = mine && pmg != 0 &&
@@ -248,16 +250,18 @@ k_obs(const SceneDev *__restrict__ scenes, StateDev st, Exports ex, Params prm, 
                         const int pm = (zmask_classes >> (3 * (int)(c & 0xffu))) & 7;
                         int lo = 0, n = 0;
                         float2 rb = make_float2(1.f, 1.f);
+                        const float relx = ra.x - px, rely = ra.y - py;
+                        const float cphi = 1.f - 2.f * ra.w * ra.w, sphi = 2.f * ra.z * ra.w;
                         if (pm) {
                             rb = __ldg(&sc.s_b[e]);
                             int hi;
-                            if (lidar_consider(lc, ra.x, ra.y, ra.z, ra.w, rb.x, rb.y, lo, hi)) {
-                                // trim the range to its first / last open ray (holes inside are skipped per ray)
+                            if (lidar_consider(lc, relx, rely, cphi, sphi, rb.x, rb.y, lo, hi)) {
+                                // trim the range to its first / last open ray (closed rays inside are clipped too)
                                 const unsigned long long m = ray_bits(lo, hi) & open_for(open, pm);
                                 if (m) { lo = __ffsll((long long)m) - 1; n = 64 - __clzll((long long)m) - lo; }
                             }
                         }
-                        lidar_expand(wp, lc, lane, lo, n, pm, (unsigned)e, ra.x, ra.y, ra.z, ra.w, rb.x, rb.y, open);
+                        lidar_expand(wp, lane, lo, n, pm, (unsigned)e, relx, rely, cphi, sphi, rb.x, rb.y);
                     }
                 }
             }
@@ -286,10 +290,10 @@ k_obs(const SceneDev *__restrict__ scenes, StateDev st, Exports ex, Params prm, 
                     bx = ra.x; by = ra.y; bqw = ra.z; bqz = ra.w; d0 = rb.x; d1 = rb.y;
                     type = (int)((__ldg(&sc.s_c[id]) >> 8) & 0xffu);
                 }
-                const float2 d = wp.raydir[i % NRAY];
+                const float2 d = wp.v.g.raydir[i % NRAY];
                 const float te = ray_box_exact(px, py, bx, by, bqw, bqz, d0, d1, d.x, d.y);
                 if (te >= 0.f) t = te;      // (a grazing ray may flip to a miss in exact arithmetic: keep the fast t)
-                const float2 xy = wp.rayxy[i % NRAY];
+                const float2 xy = wp.v.g.rayxy[i % NRAY];
                 v = make_float4(t, (float)type, __fmul_rn(t, xy.x), __fmul_rn(t, xy.y));
             }
             out[i] = v;
@@ -330,19 +334,19 @@ k_obs(const SceneDev *__restrict__ scenes, StateDev st, Exports ex, Params prm, 
         for (int pass = 0; pass < 4; pass++) {
             const int shift = 24 - 8 * pass;
             __syncwarp();
-            for (int i = lane; i < 256; i += 32) wp.hist[i] = 0;
+            for (int i = lane; i < 256; i += 32) wp.v.hist[i] = 0;
             __syncwarp();
             const unsigned hi_mask = pass == 0 ? 0u : (0xffffffffu << (shift + 8));
             for (int i = lane; i < N; i += 32) {
                 unsigned kb; bool in = true;
                 if (overflow) in = slot_key(i, kb); else kb = wp.ckey[i];
-                if (in && (kb & hi_mask) == prefix) atomicAdd(&wp.hist[(kb >> shift) & 255], 1u);
+                if (in && (kb & hi_mask) == prefix) atomicAdd(&wp.v.hist[(kb >> shift) & 255], 1u);
             }
             __syncwarp();
             // locate the bin holding the remaining-th element: lane owns bins [8*lane, 8*lane+8)
             unsigned local[8]; unsigned sum = 0;
 #pragma unroll
-            for (int k = 0; k < 8; k++) { local[k] = wp.hist[lane * 8 + k]; sum += local[k]; }
+            for (int k = 0; k < 8; k++) { local[k] = wp.v.hist[lane * 8 + k]; sum += local[k]; }
             unsigned incl = sum;
 #pragma unroll
             for (int o = 1; o < 32; o <<= 1) {
