@@ -48,6 +48,9 @@ Engine::Engine(int gpu_id, int max_agents, const Params &params, const std::vect
     if (gpu_ < 0 || gpu_ >= ndev) throw std::runtime_error("gpu_id out of range");
     GD_CUDA(cudaSetDevice(gpu_));
     GD_CUDA(cudaStreamCreateWithFlags(&stream_, cudaStreamNonBlocking));
+    GD_CUDA(cudaStreamCreateWithFlags(&copy_stream_, cudaStreamNonBlocking));
+    GD_CUDA(cudaEventCreateWithFlags(&ev_agents_, cudaEventDisableTiming));
+    GD_CUDA(cudaEventCreateWithFlags(&ev_copied_, cudaEventDisableTiming));
 
     allocExports();
 
@@ -84,6 +87,9 @@ Engine::~Engine() {
     for (void *p : arena_slabs_) cudaFree(p);
     if (d_scenes_) cudaFree(d_scenes_);
     if (h_pinned_actions_) cudaFreeHost(h_pinned_actions_);
+    if (ev_agents_) cudaEventDestroy(ev_agents_);
+    if (ev_copied_) cudaEventDestroy(ev_copied_);
+    if (copy_stream_) cudaStreamDestroy(copy_stream_);
     if (stream_) cudaStreamDestroy(stream_);
 }
 
@@ -118,6 +124,7 @@ void Engine::allocExports() {
     st_.reset_flag = devAlloc<int32_t>(owned_, W_);
     st_.stats = devAlloc<unsigned long long>(owned_, 16);
     d_worklist_ = devAlloc<int32_t>(owned_, W_);
+    d_act_stage_ = devAlloc<float>(owned_, (size_t)W_ * S_ * kActionSize);
 }
 
 void *Engine::arenaAlloc(size_t bytes) {
@@ -385,6 +392,7 @@ void Engine::launchRest(bool decrement) {
     k_agents<AGENTS_BLOCK><<<W_, AGENTS_BLOCK, smem_agents, stream_>>>(d_scenes_, st_, ex_, params_, S_,
                                                                     decrement ? 1 : 0, decrement ? 1 : 0);
     if (prof) GD_CUDA(cudaEventRecord(ev[1], stream_));
+    if (mark_agents_done_) GD_CUDA(cudaEventRecord(ev_agents_, stream_));   // reward / done / info are final here
     const int groups = (S_ + OBS_WARPS - 1) / OBS_WARPS;
     k_obs<<<W_ * groups, OBS_BLOCK, sizeof(ObsSmem), stream_>>>(d_scenes_, st_, ex_, params_, S_, groups,
                                                                 opt_knn_idx_, key_thr_);
@@ -493,13 +501,22 @@ void Engine::stepHost(const float *actions, int action_cols, float *reward, int3
     const size_t WS = (size_t)W_ * S_;
     if (action_cols <= 0 || action_cols > kActionSize) throw std::runtime_error("stepHost: action_cols must be in [1, 10]");
     if (actions) {
-        GD_CUDA(cudaMemcpy2DAsync(ex_.action, kActionSize * sizeof(float), actions, action_cols * sizeof(float),
-                                  action_cols * sizeof(float), WS, cudaMemcpyHostToDevice, stream_));
+        // one contiguous H2D into a landing buffer, then a device-side scatter into the [W,S,10] action rows
+        const size_t n = WS * (size_t)action_cols;
+        GD_CUDA(cudaMemcpyAsync(d_act_stage_, actions, n * sizeof(float), cudaMemcpyHostToDevice, stream_));
+        k_scatter_actions<<<(unsigned)((n + 255) / 256), 256, 0, stream_>>>(d_act_stage_, action_cols, ex_.action, n);
+        launches_++;
     }
+    mark_agents_done_ = true;
     stepAsync();
-    if (reward) GD_CUDA(cudaMemcpyAsync(reward, ex_.reward, WS * sizeof(float), cudaMemcpyDeviceToHost, stream_));
-    if (done) GD_CUDA(cudaMemcpyAsync(done, ex_.done, WS * sizeof(int32_t), cudaMemcpyDeviceToHost, stream_));
-    if (info) GD_CUDA(cudaMemcpyAsync(info, ex_.info, WS * kInfoSize * sizeof(int32_t), cudaMemcpyDeviceToHost, stream_));
+    mark_agents_done_ = false;
+    // k_agents has written reward / done / info; k_obs never touches them: copy them out on a second
+    // stream while the observation kernel runs
+    GD_CUDA(cudaStreamWaitEvent(copy_stream_, ev_agents_, 0));
+    if (reward) GD_CUDA(cudaMemcpyAsync(reward, ex_.reward, WS * sizeof(float), cudaMemcpyDeviceToHost, copy_stream_));
+    if (done) GD_CUDA(cudaMemcpyAsync(done, ex_.done, WS * sizeof(int32_t), cudaMemcpyDeviceToHost, copy_stream_));
+    if (info) GD_CUDA(cudaMemcpyAsync(info, ex_.info, WS * kInfoSize * sizeof(int32_t), cudaMemcpyDeviceToHost, copy_stream_));
+    GD_CUDA(cudaStreamSynchronize(copy_stream_));
     sync();
 }
 

@@ -166,6 +166,10 @@ private:
     std::vector<void *> owned_;
     int32_t *d_worklist_ = nullptr;   // [W] scratch for reset lists
     float *h_pinned_actions_ = nullptr;
+    float *d_act_stage_ = nullptr;        // [W*S*10] contiguous landing buffer of stepHost's actions
+    cudaStream_t copy_stream_ = nullptr;  // stepHost: reward / done / info leave while k_obs still runs
+    cudaEvent_t ev_agents_ = nullptr, ev_copied_ = nullptr;
+    bool mark_agents_done_ = false;
     int kernels_per_step_ = 0;
     uint64_t launches_ = 0;
     uint64_t steps_ = 0, episodes_reset_ = 0;

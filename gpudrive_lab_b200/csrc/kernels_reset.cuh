@@ -153,4 +153,13 @@ __global__ void k_reset(const int32_t *__restrict__ worlds, const SceneDev *__re
     ex.response[wa] = resp;
 }
 
+// stepHost: contiguous [W*S, cols] host actions -> the first `cols` columns of the [W*S, 10] action rows
+__global__ void k_scatter_actions(const float *__restrict__ src, int cols, float *__restrict__ action, size_t n)
+{
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const size_t row = i / (size_t)cols;
+    action[row * kActionSize + (i - row * (size_t)cols)] = src[i];
+}
+
 } // namespace gd

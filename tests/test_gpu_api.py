@@ -1,0 +1,94 @@
+"""C-ABI entry points that have no reference equivalent (host-buffer step, async step, device scenario
+pool, statistics, kernel timing) behave like the reference-shaped calls they wrap."""
+import numpy as np
+import pytest
+
+from golden_util import unpack
+from helpers import engine_params, param_dict, random_actions
+
+pytestmark = pytest.mark.gpu
+
+
+def _sim(scenes, pd, S=128):
+    import torch
+    assert torch.cuda.is_available()
+    from gpudrive_lab_b200 import madrona_gpudrive as mg
+    return mg.SimManager(mg.madrona.ExecMode.CUDA, 0, scenes, engine_params(pd), max_agents=S)
+
+
+def test_step_host_equals_step(tmp_path):
+    import torch
+    scenes = unpack(["synth_a", "synth_b", "synth_a"], tmp_path)
+    pd = param_dict(dynamicsModel=2, enableLidar=True, collisionBehaviour=0, maxNumControlledAgents=8)
+    a, b = _sim(scenes, pd), _sim(scenes, pd)
+    W, S = 3, 128
+    h_rew = torch.empty(W, S, 1).pin_memory()
+    h_done = torch.empty(W, S, 1, dtype=torch.int32).pin_memory()
+    h_info = torch.empty(W, S, 5, dtype=torch.int32).pin_memory()
+    act_b = b.action_tensor().to_torch()
+    for t in range(12):
+        act = random_actions(t, W, S, 2, seed=3)
+        h_act = torch.from_numpy(np.ascontiguousarray(act[..., :3])).pin_memory()
+        a.step_host(h_act, h_rew, h_done, h_info)
+        act_b[:, :, :3].copy_(torch.from_numpy(act[..., :3]))
+        torch.cuda.synchronize()
+        b.step()
+        assert torch.equal(h_rew, b.reward_tensor().to_torch().cpu())
+        assert torch.equal(h_done, b.done_tensor().to_torch().cpu())
+        assert torch.equal(h_info, b.info_tensor().to_torch().cpu())
+        for name in ("self_observation_tensor", "partner_observations_tensor", "agent_roadmap_tensor", "lidar_tensor"):
+            assert torch.equal(getattr(a, name)().to_torch(), getattr(b, name)().to_torch()), name
+    # action columns beyond those passed stay untouched (zero after reset)
+    assert float(a.action_tensor().to_torch()[:, :, 3:].abs().sum()) == 0.0
+
+
+def test_async_step_and_kernel_times(tmp_path):
+    import torch
+    scenes = unpack(["synth_b"], tmp_path)
+    pd = param_dict(dynamicsModel=1)
+    a, b = _sim(scenes, pd), _sim(scenes, pd)
+    a.set_option(1, 1)
+    n0 = a.launch_count()
+    for _ in range(5):
+        a.step_async()
+    a.sync()
+    for _ in range(5):
+        b.step()
+    assert a.launch_count() - n0 == 10            # two kernels per step
+    kt = a.kernel_times()
+    assert kt["steps"] == 5 and kt["k_obs_ms"] > 0 and kt["k_agents_ms"] > 0
+    assert torch.equal(a.absolute_self_observation_tensor().to_torch(), b.absolute_self_observation_tensor().to_torch())
+    st = a.stats()
+    assert st["steps"] == 5 and st["agent_steps"] == 5 * int(a.shape_tensor().to_torch()[0, 0])
+
+
+def test_device_scenario_pool_rebind(tmp_path):
+    """Re-binding a world to a pooled scenario gives the same tensors as constructing it there."""
+    import torch
+    sa, sb = unpack(["synth_a", "synth_b"], tmp_path)
+    pd = param_dict(dynamicsModel=2, maxNumControlledAgents=8)
+    sim = _sim([sa, sa], pd)
+    ida, idb = sim.pool_add(sa), sim.pool_add(sb)
+    assert ida != idb
+    for _ in range(3):
+        sim.step()
+    sim.bind_worlds([1], [idb])          # world 1 now runs scenario b, freshly reset
+    ref = _sim([sa, sb], pd)
+    for name in ("shape_tensor", "map_observation_tensor", "expert_trajectory_tensor", "controlled_state_tensor",
+                 "self_observation_tensor", "agent_roadmap_tensor", "partner_observations_tensor", "done_tensor",
+                 "steps_remaining_tensor", "info_tensor", "metadata_tensor", "world_means_tensor"):
+        x, y = getattr(sim, name)().to_torch()[1], getattr(ref, name)().to_torch()[1]
+        assert torch.equal(x, y), name
+    assert int(sim.steps_remaining_tensor().to_torch()[0, 0, 0]) == 91 - 3      # world 0 untouched
+
+
+def test_errors_are_reported_not_fatal(tmp_path):
+    scenes = unpack(["synth_a"], tmp_path)
+    sim = _sim(scenes, param_dict())
+    with pytest.raises(RuntimeError):
+        sim.set_maps(scenes + scenes)                 # length must equal num_worlds (src/mgr.cpp:592)
+    with pytest.raises(RuntimeError):
+        sim.bev_observation_tensor()
+    with pytest.raises(RuntimeError):
+        sim.reset([5])
+    sim.step()                                        # the handle is still usable
