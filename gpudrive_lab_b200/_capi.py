@@ -29,7 +29,7 @@ class GdParams(C.Structure):
 
 
 class GdConfig(C.Structure):
-    _fields_ = [("gpu_id", C.c_int32), ("max_agents", C.c_int32), ("params", GdParams)]
+    _fields_ = [("gpu_id", C.c_int32), ("max_agents", C.c_int32), ("params", GdParams), ("flags", C.c_int32)]
 
 
 class GdTensorDesc(C.Structure):

@@ -47,7 +47,7 @@ int gd_create(const GdConfig *cfg, const char *const *scenes, int32_t n_scenes, 
         if (!cfg || !scenes || !out) throw std::runtime_error("gd_create: null argument");
         std::vector<std::string> v;
         for (int i = 0; i < n_scenes; i++) v.emplace_back(scenes[i]);
-        *out = new gd::Engine(cfg->gpu_id, cfg->max_agents, toParams(&cfg->params), v);
+        *out = new gd::Engine(cfg->gpu_id, cfg->max_agents, toParams(&cfg->params), v, cfg->flags);
     })
 }
 

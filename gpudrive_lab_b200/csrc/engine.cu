@@ -7,6 +7,7 @@
 #include <cstring>
 #include <stdexcept>
 
+#include "kernels_bev.cuh"
 #include "kernels_obs_main.cuh"
 #include "kernels_reset.cuh"
 #include "kernels_step.cuh"
@@ -34,8 +35,8 @@ static T *devAlloc(std::vector<void *> &owned, size_t count, int fill_byte = 0) 
     return static_cast<T *>(p);
 }
 
-Engine::Engine(int gpu_id, int max_agents, const Params &params, const std::vector<std::string> &scenes)
-    : gpu_(gpu_id), W_((int)scenes.size()), S_(max_agents), params_(params)
+Engine::Engine(int gpu_id, int max_agents, const Params &params, const std::vector<std::string> &scenes, int flags)
+    : gpu_(gpu_id), W_((int)scenes.size()), S_(max_agents), bev_enabled_((flags & 1) != 0), params_(params)
 {
     if (W_ <= 0) throw std::runtime_error("SimManager needs at least one scene (num_worlds = len(scenes))");
     if (S_ < 2 || S_ > 128) throw std::runtime_error("max_agents must be in [2, 128]");
@@ -70,6 +71,8 @@ Engine::Engine(int gpu_id, int max_agents, const Params &params, const std::vect
     GD_CUDA(cudaMemcpy(st_.world_scene, world_scene_.data(), W_ * sizeof(int32_t), cudaMemcpyHostToDevice));
 
     GD_CUDA(cudaFuncSetAttribute(k_obs, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(ObsSmem)));
+    if (bev_enabled_)
+        GD_CUDA(cudaFuncSetAttribute(k_bev, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(BevSmem)));
 
     // Sim::Sim -> createPersistentEntities + initWorld for every world, then Manager's ctor reset({})
     std::vector<int32_t> all(W_);
@@ -116,6 +119,7 @@ void Engine::allocExports() {
     ex_.map_name = devAlloc<int32_t>(owned_, (size_t)W_ * 32);
     ex_.scenario_id = devAlloc<int32_t>(owned_, (size_t)W_ * 32);
     ex_.valid_state = devAlloc<int32_t>(owned_, WS);
+    ex_.bev = bev_enabled_ ? devAlloc<float>(owned_, WS * (size_t)(BEV_RES * BEV_RES)) : nullptr;
     ex_.knn_idx = devAlloc<int32_t>(owned_, WS * kMaxAgentMapObs, 0xff);
     st_.pos = devAlloc<float4>(owned_, WS);
     st_.rv = devAlloc<float4>(owned_, WS);
@@ -399,6 +403,10 @@ void Engine::launchRest(bool decrement) {
     if (prof) { GD_CUDA(cudaEventRecord(ev[2], stream_)); prof_pending_++; }
     launches_ += 2;
     kernels_per_step_ = 2;
+    if (bev_enabled_) {
+        k_bev<<<W_ * S_, BEV_BLOCK, sizeof(BevSmem), stream_>>>(d_scenes_, st_, ex_, params_, S_, key_thr_);
+        launches_++; kernels_per_step_ = 3;
+    }
     GD_CUDA(cudaGetLastError());
 }
 
@@ -601,8 +609,11 @@ TensorDesc Engine::tensor(int id) const {
     case T_SCENARIO_ID: set(ex_.scenario_id, 1, {W, 32}); break;
     case T_KNN_IDX: set(ex_.knn_idx, 1, {W, S, kMaxAgentMapObs}); break;
     case T_BEV:
-        throw std::runtime_error("bev_observation_tensor: BEV rasterisation is not built in this engine yet "
-                                 "(160 KB per agent slot; optional row 8(f)-2)");
+        if (!bev_enabled_)
+            throw std::runtime_error("bev_observation_tensor: the bird's-eye-view grid is opt-in (160 KB per agent "
+                                     "slot): create the manager with GdConfig.flags |= GD_FLAG_BEV / enable_bev=True");
+        set(ex_.bev, 0, {W, S, BEV_RES, BEV_RES, 1});
+        break;
     default: throw std::runtime_error("unknown tensor id");
     }
     return d;

@@ -69,6 +69,7 @@ struct Exports {
     int32_t *map_name;    // [W,32]
     int32_t *scenario_id; // [W,32]
     int32_t *valid_state; // [W,S,1] (never written by the reference)
+    float *bev;           // [W,S,200,200,1] only with GD_FLAG_BEV (else null)
     int32_t *knn_idx;     // [W,S,200] debug side buffer: road-entity index per roadmap row, -1 pad
 };
 
@@ -106,7 +107,7 @@ struct StepStats {      // gd_stats
 
 class Engine {
 public:
-    Engine(int gpu_id, int max_agents, const Params &params, const std::vector<std::string> &scenes);
+    Engine(int gpu_id, int max_agents, const Params &params, const std::vector<std::string> &scenes, int flags = 0);
     ~Engine();
 
     void step();                 // launch + sync (reference semantics, src/mgr.cpp:569-580)
@@ -147,6 +148,7 @@ private:
     void allocExports();
 
     int gpu_, W_, S_;
+    bool bev_enabled_ = false;
     Params params_;
     cudaStream_t stream_ = nullptr;
     std::vector<std::string> scene_paths_;            // per world

@@ -7,7 +7,8 @@
 Same names, argument meaning and tensor layouts as the reference. Differences, all explicit:
   * ExecMode.CPU raises: this engine has no CPU path (the reference's CPU mode is oracle/_ref).
   * enable_batch_renderer=True, rgb_tensor(), depth_tensor() raise: no graphics stack on this box.
-  * bev_observation_tensor() raises (BEV rasterisation is an optional later row).
+  * bev_observation_tensor() needs SimManager(..., enable_bev=True): the grid is 160 KB per agent slot,
+    so it is opt-in here (the reference always computes it).
   * agent_roadmap rows come in road-entity index order (the reference's order is the internal
     heap order, which already differs between its debug and release builds); the set of rows per
     agent is identical. knn_index_tensor() gives the road-entity index of every row.
@@ -149,7 +150,7 @@ class SimManager:
     """src/bindings.cpp:91-149. num_worlds = len(scenes); the constructor performs the first reset."""
 
     def __init__(self, exec_mode, gpu_id, scenes, params, enable_batch_renderer=False,
-                 batch_render_view_width=64, batch_render_view_height=64, max_agents=None):
+                 batch_render_view_width=64, batch_render_view_height=64, max_agents=None, enable_bev=False):
         if int(exec_mode) != int(_ExecMode.CUDA):
             raise RuntimeError("gpudrive_lab_b200 implements ExecMode.CUDA only; there is no CPU fallback")
         if enable_batch_renderer:
@@ -158,7 +159,7 @@ class SimManager:
         self._lib = lib
         self._h = C.c_void_p()
         cfg = _capi.GdConfig(int(gpu_id), int(max_agents if max_agents is not None else kMaxAgentCount),
-                             params._to_c())
+                             params._to_c(), 1 if enable_bev else 0)
         arr = (C.c_char_p * len(scenes))(*[str(s).encode() for s in scenes])
         _capi.check(lib.gd_create(C.byref(cfg), arr, len(scenes), C.byref(self._h)))
         self.num_worlds = len(scenes)

@@ -49,7 +49,13 @@ typedef struct GdConfig {
     int32_t gpu_id;
     int32_t max_agents;
     GdParams params;
+    int32_t flags;      /* GD_FLAG_* */
 } GdConfig;
+
+/* GD_FLAG_BEV: allocate and compute bev_observation_tensor every step (collectBevObservationsSystem,
+ * src/sim.cpp:462-555). The reference always does; here it is opt-in because the export is 160 KB per agent
+ * slot (W x S x 200 x 200 floats: 21 GB at 1024 worlds, more than one GPU holds at 8192). */
+enum GdFlags { GD_FLAG_BEV = 1 };
 
 typedef void *GdHandle;
 
@@ -63,7 +69,7 @@ enum GdTensorId {
     GD_T_PARTNER_OBSERVATIONS,  /* partner_observations_tensor      f32 [W,S,S-1,9]   */
     GD_T_AGENT_ROADMAP,         /* agent_roadmap_tensor             f32 [W,S,200,9]   */
     GD_T_LIDAR,                 /* lidar_tensor                     f32 [W,S,3,50,4]  */
-    GD_T_BEV_OBSERVATION,       /* bev_observation_tensor           (not built: returns an error) */
+    GD_T_BEV_OBSERVATION,       /* bev_observation_tensor           f32 [W,S,200,200,1] (needs GD_FLAG_BEV) */
     GD_T_STEPS_REMAINING,       /* steps_remaining_tensor           i32 [W,S,1]       */
     GD_T_SHAPE,                 /* shape_tensor                     i32 [W,2]         */
     GD_T_CONTROLLED_STATE,      /* controlled_state_tensor          i32 [W,S,1]       */

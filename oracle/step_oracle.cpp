@@ -10,6 +10,7 @@
 //   self / absolute / partner observations      src/sim.cpp:168-240,769-783
 //   agent road map (kNN heap and linear)        src/sim.cpp:242-280, src/knn.hpp:15-158
 //   lidar                                       src/sim.cpp:394-460, broadphase.cpp:656-888, math.inl:1575-1601
+//   bird's-eye-view grid                        src/sim.cpp:462-555, src/rasterizer.hpp:12-78
 //   reset                                       src/level_gen.cpp:467-521, src/level_gen.hpp:16-38
 // Scene construction (JSON -> entities, rows a16/a17 of SURVEY.md section 8) is NOT restated here: the
 // oracle takes the entity tables as arrays. Those tables are pinned separately against the reference
@@ -115,7 +116,8 @@ struct World {
     std::vector<Agent> agents;
     std::vector<float> traj;
     // exports, reference layouts for one world
-    std::vector<float> action, reward, self_obs, partner, roadmap, lidar, abs_obs;
+    std::vector<float> action, reward, self_obs, partner, roadmap, lidar, abs_obs, bev;
+    bool want_bev = false;
     std::vector<int32_t> done, steps, info, controlled, response, knn_index;
 };
 
@@ -545,6 +547,63 @@ void lidar_obs(World &w) {
     }
 }
 
+// ---------------------------------------------------------------- bird's-eye-view grid
+constexpr int BEV_RES = 200;      // consts::bev_rasterization_resolution, src/consts.hpp:49
+
+// rasterizer::toGridCoords + rasterizeRotatedRectangle, src/rasterizer.hpp:12-78
+void rasterize(float *grid, float cx, float cy, float yaw, float length, float width, size_t type, float radius) {
+    const int resolution = BEV_RES;
+    float half_w = width / 2.0f, half_l = length / 2.0f;
+    float scale_px = (2 * radius) / resolution;
+    float scale_m = resolution / (2 * radius);
+    int gx = static_cast<int>((cx + radius) * scale_m), gy = static_cast<int>((cy + radius) * scale_m);
+    gx = std::min(std::max(0, gx), resolution - 1); gy = std::min(std::max(0, gy), resolution - 1);
+    float max_side = std::max(half_w, half_l);
+    int box_radius = static_cast<int>(std::ceil(std::sqrt(2 * (max_side * max_side)) / scale_px));
+    float cos_yaw = std::cos(-yaw), sin_yaw = std::sin(-yaw);
+    for (int dy = -box_radius; dy <= box_radius; dy++) {
+        for (int dx = -box_radius; dx <= box_radius; dx++) {
+            int x = gx + dx, y = gy + dy;
+            if (x < 0 || x >= resolution || y < 0 || y >= resolution) continue;
+            float px = x * scale_px - radius, py = y * scale_px - radius;
+            float ldx = px - cx, ldy = py - cy;
+            float local_x = ldx * cos_yaw - ldy * sin_yaw;
+            float local_y = ldx * sin_yaw + ldy * cos_yaw;
+            constexpr float epsilon = 1e-3f;
+            if (std::abs(local_x) <= half_l + epsilon && std::abs(local_y) <= half_w + epsilon)
+                grid[(size_t)y * resolution + x] = (float)type;
+        }
+    }
+}
+
+// collectBevObservationsSystem, src/sim.cpp:462-555
+void bev_obs(World &w) {
+    if (w.prm.disableClassicalObs || !w.want_bev) return;
+    const float radius = w.prm.observationRadius;
+    for (int a = 0; a < w.A; a++) {
+        const Agent &g = w.agents[a];
+        float *grid = &w.bev[(size_t)a * BEV_RES * BEV_RES];
+        std::fill(grid, grid + BEV_RES * BEV_RES, 0.f);
+        int arr = 0;
+        for (int r = 0; r < w.R && arr < K_ROADMAP; r++) {
+            MapRow m = observation_of(g, w.roads[r], r);
+            if (sqrtf(length2_xy(m.v[0], m.v[1])) > radius) continue;
+            float d1 = std::max(m.v[3], (2 * radius / BEV_RES));        // minimum segment width
+            rasterize(grid, m.v[0], m.v[1], m.v[5], m.v[2], d1, (size_t)m.v[6], radius);
+            arr++;
+        }
+        for (int j = 0; j < w.A; j++) {
+            if (j == a) continue;
+            const Agent &o = w.agents[j];
+            V3 d = o.pos - g.pos;
+            V3 rel = rotate(inv(g.rot), {d.x, d.y, 0.f});
+            float heading = quat_to_yaw(mul(inv(g.rot), o.rot));
+            if (sqrtf(length2_xy(rel.x, rel.y)) > radius) continue;
+            rasterize(grid, rel.x, rel.y, heading, o.vsize.x, o.vsize.y, (size_t)o.type, radius);
+        }
+    }
+}
+
 // setupRestOfTasks, src/sim.cpp:785-943
 void rest_of_step(World &w, bool decrement) {
     collisions(w);
@@ -553,6 +612,7 @@ void rest_of_step(World &w, bool decrement) {
     partner_obs(w);
     roadmap_obs(w);
     lidar_obs(w);
+    bev_obs(w);
 }
 
 // resetAgent + resetAgentInterface + getZeroAction: src/level_gen.cpp:23-54, src/level_gen.hpp:16-38
@@ -624,6 +684,13 @@ void *gdo_create(const void *params, int S, int A, int R, const float *agent_sta
     rest_of_step(*w, false);      // the constructor's Reset graph (src/mgr.cpp:565, src/sim.cpp:953-957)
     return w;
 }
+// switches the bird's-eye-view grid on (160 KB per agent slot) and computes it for the current state
+void gdo_enable_bev(void *h) {
+    World &w = *static_cast<World *>(h);
+    w.want_bev = true;
+    w.bev.assign((size_t)w.S * BEV_RES * BEV_RES, 0.f);
+    bev_obs(w);
+}
 void gdo_destroy(void *h) { delete static_cast<World *>(h); }
 void gdo_step(void *h) { World &w = *static_cast<World *>(h); movement(w); rest_of_step(w, true); }
 // resets this world (do_reset != 0) and runs the Reset graph, which recomputes every world (sim.cpp:953-957)
@@ -632,14 +699,14 @@ void gdo_reset(void *h, int do_reset) {
     if (do_reset) reset_world(w);
     rest_of_step(w, false);
 }
-// tensor ids: 0 action 1 reward 2 self_obs 3 partner 4 roadmap 5 lidar 6 abs_obs | 16 done 17 steps 18 info
+// tensor ids: 0 action 1 reward 2 self_obs 3 partner 4 roadmap 5 lidar 6 abs_obs 7 bev | 16 done 17 steps 18 info
 // 19 controlled 20 response 21 knn_index
 void *gdo_tensor(void *h, int id) {
     World &w = *static_cast<World *>(h);
     switch (id) {
     case 0: return w.action.data(); case 1: return w.reward.data(); case 2: return w.self_obs.data();
     case 3: return w.partner.data(); case 4: return w.roadmap.data(); case 5: return w.lidar.data();
-    case 6: return w.abs_obs.data(); case 16: return w.done.data(); case 17: return w.steps.data();
+    case 6: return w.abs_obs.data(); case 7: return w.bev.data(); case 16: return w.done.data(); case 17: return w.steps.data();
     case 18: return w.info.data(); case 19: return w.controlled.data(); case 20: return w.response.data();
     case 21: return w.knn_index.data();
     }

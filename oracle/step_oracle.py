@@ -17,11 +17,12 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 LIB = os.path.join(HERE, "_build", "libgd_oracle.so")
 
 _F32 = {"action": (0, 10), "reward": (1, 1), "self_observation": (2, 8), "partner_observations": (3, None),
-        "agent_roadmap": (4, 200 * 9), "lidar": (5, 3 * 50 * 4), "absolute_self_observation": (6, 14)}
+        "agent_roadmap": (4, 200 * 9), "lidar": (5, 3 * 50 * 4), "absolute_self_observation": (6, 14), "bev_observation": (7, 200 * 200)}
 _I32 = {"done": (16, 1), "steps_remaining": (17, 1), "info": (18, 5), "controlled_state": (19, 1),
         "response_type": (20, 1), "knn_index": (21, 200)}
 _SHAPES = {"partner_observations": lambda S: (S, S - 1, 9), "agent_roadmap": lambda S: (S, 200, 9),
-           "lidar": lambda S: (S, 3, 50, 4), "knn_index": lambda S: (S, 200)}
+           "lidar": lambda S: (S, 3, 50, 4), "knn_index": lambda S: (S, 200),
+           "bev_observation": lambda S: (S, 200, 200, 1)}
 
 _lib = None
 
@@ -43,6 +44,7 @@ def load():
         lib.gdo_destroy.argtypes = [C.c_void_p]
         lib.gdo_step.argtypes = [C.c_void_p]
         lib.gdo_reset.argtypes = [C.c_void_p, C.c_int]
+        lib.gdo_enable_bev.argtypes = [C.c_void_p]
         lib.gdo_tensor.restype = C.c_void_p
         lib.gdo_tensor.argtypes = [C.c_void_p, C.c_int]
         lib.gdo_obb_collided.argtypes = [C.c_void_p, C.c_void_p]
@@ -104,6 +106,10 @@ class OracleManager:
                 cache[s] = scene_host.scene_tensors(s, params, S)
             self.worlds.append(OracleWorld(cache[s], self._cp, S))
         self.num_worlds = len(self.worlds)
+
+    def enable_bev(self):
+        for w in self.worlds:
+            w._lib.gdo_enable_bev(w._h)
 
     def step(self):
         for w in self.worlds:

@@ -264,11 +264,13 @@ class EngineAdapter:
                 "absolute_self_observation": "absolute_self_observation_tensor",
                 "steps_remaining": "steps_remaining_tensor", "controlled_state": "controlled_state_tensor",
                 "response_type": "response_type_tensor", "knn_index": "knn_index_tensor",
-                "map_observation": "map_observation_tensor", "expert_trajectory": "expert_trajectory_tensor"}
+                "map_observation": "map_observation_tensor", "expert_trajectory": "expert_trajectory_tensor",
+                "bev_observation": "bev_observation_tensor"}
 
-    def __init__(self, scenes, pd, S=128):
+    def __init__(self, scenes, pd, S=128, enable_bev=False):
         from gpudrive_lab_b200 import madrona_gpudrive as mg
-        self.sim = mg.SimManager(mg.madrona.ExecMode.CUDA, 0, scenes, engine_params(pd), max_agents=S)
+        self.sim = mg.SimManager(mg.madrona.ExecMode.CUDA, 0, scenes, engine_params(pd), max_agents=S,
+                                 enable_bev=enable_bev)
         self._act = self.sim.action_tensor().to_torch()
 
     def tensor(self, name):

@@ -88,3 +88,27 @@ def test_oracle_matches_reference_live(tmp_path):
         compare_step(snapshot_ref(ref), kat._snapshot(mgr, TENSORS_CMP), 50.0, True, tag=f"step {t + 1}",
                      stats=stats)
     ref.close()
+
+
+def test_bev_matches_reference_live(tmp_path):
+    """The restated bird's-eye-view rasteriser (src/sim.cpp:462-555, src/rasterizer.hpp:12-78) is
+    bit-identical to the reference's on a synthetic and on the reference's own test scene."""
+    from oracle import refmgr
+    if not refmgr.available():
+        pytest.skip("oracle/_ref not built")
+    from oracle.step_oracle import OracleManager
+    scenes = unpack(["synth_b", "womd_test_scene"], tmp_path)
+    pd = param_dict(dynamicsModel=1, maxNumControlledAgents=6, observationRadius=40.0)
+    ref = refmgr.RefManager(scenes, ref_params(pd))
+    mgr = OracleManager(scenes, engine_params(pd))
+    mgr.enable_bev()
+    A = ref.tensor("shape")[:, 0]
+    for t in range(4):
+        for w in range(2):
+            r, o = ref.tensor("bev_observation")[w, :A[w]], mgr.tensor("bev_observation")[w, :A[w]]
+            assert (r != 0).sum() > 1000 and np.array_equal(r, o), (t, w)
+        a = random_actions(t, 2, 128, 1, seed=2)
+        ref.tensor("action")[...] = a
+        mgr.set_actions(a)
+        ref.step(); mgr.step()
+    ref.close()

@@ -79,3 +79,28 @@ def test_knn_index_sets_bit_exact(tmp_path):
                 kk = ke[w, i][ke[w, i] >= 0]
                 assert len(set(kk.tolist())) == len(kk)
     assert ties <= 2
+
+
+def test_bev_grid_bit_exact(tmp_path):
+    """collectBevObservationsSystem (a14): the 200 x 200 grid of every live agent equals the oracle's,
+    which is bit-identical to the reference's (tests/test_cpu_oracle.py::test_bev_matches_reference_live)."""
+    from oracle.step_oracle import OracleManager
+    scenes = unpack(["synth_b", "womd_test_scene", "synth_a"], tmp_path)
+    pd = param_dict(dynamicsModel=1, maxNumControlledAgents=6, observationRadius=40.0)
+    orc = OracleManager(scenes, engine_params(pd))
+    orc.enable_bev()
+    eng = EngineAdapter(scenes, pd, enable_bev=True)
+    shape = orc.tensor("shape")
+    for t in range(8):
+        go, ge = orc.tensor("bev_observation"), eng.tensor("bev_observation")
+        assert ge.shape == (3, 128, 200, 200, 1)
+        for w in range(3):
+            A = int(shape[w, 0])
+            assert (go[w, :A] != 0).sum() > 1000
+            assert np.array_equal(go[w, :A], ge[w, :A]), (t, w, int((go[w, :A] != ge[w, :A]).sum()))
+            assert not ge[w, A:].any()
+        a = random_actions(t, 3, 128, 1, seed=9)
+        orc.set_actions(a); eng.set_actions(a)
+        orc.step(); eng.step()
+        if t == 4:
+            orc.reset([0, 2]); eng.reset([0, 2])
