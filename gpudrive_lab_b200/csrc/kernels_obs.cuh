@@ -226,6 +226,7 @@ __device__ __forceinline__ void lidar_expand(ObsWarpSmem &wp, int lane, int lo, 
                                              float relx, float rely, float cphi, float sphi, float d0, float d1)
 {
     const unsigned FULL = 0xffffffffu;
+    if (!__any_sync(FULL, n > 0)) return;
     int incl = n;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
@@ -234,7 +235,6 @@ __device__ __forceinline__ void lidar_expand(ObsWarpSmem &wp, int lane, int lo, 
     }
     const int total = __shfl_sync(FULL, incl, 31);
     GD_CNT(5, total); GD_CNT(6, 1);
-    if (total == 0) return;
     const int excl = incl - n;
     // ray origin in the box frame (the box centre is (relx, rely) away from the origin)
     const float opx = -fmaf(cphi, relx, sphi * rely), opy = -fmaf(cphi, rely, -(sphi * relx));
@@ -299,7 +299,12 @@ __device__ __forceinline__ void flush_rows(float *stage, float *dst, const float
         for (int k = 0; k < 9; k++) stage[rank * 9 + k] = row[k];
     }
     __syncwarp();
-    for (int i = lane; i < m * 9; i += 32) dst[i] = stage[i];
+    const int n = m * 9;
+#pragma unroll
+    for (int k = 0; k < 9; k++) {
+        const int i = lane + 32 * k;
+        if (i < n) dst[i] = stage[i];
+    }
     __syncwarp();
 }
 

@@ -162,6 +162,7 @@ k_obs(const SceneDev *__restrict__ scenes, StateDev st, Exports ex, Params prm, 
         // ---- one lane per group: can its bounding circle matter to this agent?
         const int gN = min(OBS_GCAP, G - g0);
         int nlist = 0;
+        unsigned band_planes = 0, band_near = 0;     // per band: lidar planes / kNN interest of its groups
         __syncwarp();
         for (int base = 0; base < gN; base += 32) {
             const int gl = base + lane;
@@ -195,6 +196,9 @@ k_obs(const SceneDev *__restrict__ scenes, StateDev st, Exports ex, Params prm, 
             const unsigned km = __ballot_sync(FULL, keep);
             if (keep) wp.v.g.glist[nlist + __popc(km & lt_mask)] = desc;
             nlist += __popc(km);
+            const unsigned bsh = (desc >> 12) & 7u;
+            band_planes |= __reduce_or_sync(FULL, keep ? ((desc >> 28) << (3u * bsh)) : 0u);
+            band_near |= __reduce_or_sync(FULL, (keep && ((desc >> 27) & 1u)) ? (1u << bsh) : 0u);
         }
         __syncwarp();
         GD_CNT(0, 1); GD_CNT(1, nlist);
@@ -205,6 +209,10 @@ k_obs(const SceneDev *__restrict__ scenes, StateDev st, Exports ex, Params prm, 
             if (lidar_on) open_rays(wp.u.l.bt, band_lo * 0.9999f - 1e-3f, lane, open);
             const bool any_open = lidar_on && (open[0] | open[1] | open[2]) != 0ull;
             if (!any_open && !(want_cands && band_lo <= rpad)) break;     // nothing farther can matter
+            {   // no group of this band is near, and none lies on a plane that still has open rays: skip it
+                const unsigned planes_open = (open[0] ? 1u : 0u) | (open[1] ? 2u : 0u) | (open[2] ? 4u : 0u);
+                if (!(((band_planes >> (3 * band)) & planes_open) || ((band_near >> band) & 1u))) continue;
+            }
             for (int base = 0; base < nlist; base += 32) {
                 const int li = base + lane;
                 const uint32_t desc = li < nlist ? wp.v.g.glist[li] : 0u;
@@ -328,8 +336,74 @@ k_obs(const SceneDev *__restrict__ scenes, StateDev st, Exports ex, Params prm, 
     const bool take_all = cnt <= K;
     const int N = overflow ? RS : C;
 
-    if (!take_all) {
-        // exact radix select (4 x 8 bits, MSB first) of the K-th smallest key among in-radius entities
+    bool selected = take_all;
+    if (!take_all && !overflow) {
+        // Fast path: one histogram pass over a monotone 8-bit quantisation of the key finds the bin that
+        // holds the K-th smallest; its (few) members are then ranked exactly by (key, road index).
+        const float qscale = key_thr > 0.f ? 255.9f / key_thr : 0.f;
+        auto quant = [&](unsigned kb) -> int {
+            return first_k_only ? min(255, (int)(kb >> 6)) : min(255, __float2int_rz(__uint_as_float(kb) * qscale));
+        };
+        __syncwarp();
+        for (int i = lane; i < 256; i += 32) wp.v.hist[i] = 0;
+        __syncwarp();
+        for (int i = lane; i < C; i += 32) atomicAdd(&wp.v.hist[quant(wp.ckey[i])], 1u);
+        __syncwarp();
+        unsigned local[8]; unsigned sum = 0;
+#pragma unroll
+        for (int k = 0; k < 8; k++) { local[k] = wp.v.hist[lane * 8 + k]; sum += local[k]; }
+        unsigned incl = sum;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            unsigned v = __shfl_up_sync(FULL, incl, o);
+            if (lane >= o) incl += v;
+        }
+        const unsigned excl = incl - sum;
+        const bool mine = (unsigned)K > excl && (unsigned)K <= incl;
+        int digit = 0, before = 0, inbin = 0;
+        if (mine) {
+            unsigned acc = excl;
+#pragma unroll
+            for (int k = 0; k < 8; k++) {
+                if ((unsigned)K > acc && (unsigned)K <= acc + local[k]) { digit = lane * 8 + k; before = (int)acc; inbin = (int)local[k]; }
+                acc += local[k];
+            }
+        }
+        const int src = __ffs(__ballot_sync(FULL, mine)) - 1;
+        digit = __shfl_sync(FULL, digit, src);
+        before = __shfl_sync(FULL, before, src);
+        inbin = __shfl_sync(FULL, inbin, src);
+        if (inbin <= 32) {
+            uint32_t *mk = reinterpret_cast<uint32_t *>(wp.u.stage), *mi = mk + 32;
+            int nm = 0;
+            for (int base = 0; base < C; base += 32) {
+                const int i = base + lane;
+                const bool is = i < C && quant(wp.ckey[i]) == digit;
+                const unsigned bm = __ballot_sync(FULL, is);
+                if (is) {
+                    const int slot = nm + __popc(bm & lt_mask);
+                    mk[slot] = wp.ckey[i];
+                    mi[slot] = __ldg(&sc.s_c[wp.cpos[i]]) >> 16;
+                }
+                nm += __popc(bm);
+            }
+            __syncwarp();
+            const unsigned myk = lane < nm ? mk[lane] : 0xffffffffu, myi = lane < nm ? mi[lane] : 0xffffffffu;
+            int less = 0;
+            for (int m = 0; m < nm; m++) {
+                const unsigned k2 = mk[m], i2 = mi[m];
+                less += (k2 < myk || (k2 == myk && i2 < myi)) ? 1 : 0;
+            }
+            const int hit = __ffs(__ballot_sync(FULL, lane < nm && less == K - before - 1)) - 1;
+            thr = __shfl_sync(FULL, myk, hit);
+            idx_thr = __shfl_sync(FULL, myi, hit);
+            selected = true;
+            __syncwarp();
+        }
+    }
+    if (!selected) {
+        // general path (candidate overflow, or many equal keys): exact radix select (4 x 8 bits, MSB first)
+        // of the K-th smallest key among in-radius entities
         unsigned prefix = 0; int remaining = K; int count_eq = 0;
         for (int pass = 0; pass < 4; pass++) {
             const int shift = 24 - 8 * pass;

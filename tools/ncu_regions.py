@@ -12,12 +12,12 @@ for r in rows:
     k = (cur, int(r[0])); v = data.get(k, (0, 0))
     data[k] = (v[0] + int(r[si] or 0), v[1] + int(r[ie] or 0))
 M, O = "kernels_obs_main.cuh", "kernels_obs.cuh"
-regions = [("staging/self/abs", M, 1, 73), ("partner rows", M, 74, 105), ("lidar setup + agents", M, 106, 151),
-           ("group list", M, 152, 198), ("band loop control", M, 199, 227), ("knn sweep", M, 228, 246),
-           ("lidar per entity", M, 247, 268), ("lidar write-out", M, 269, 299), ("select", M, 300, 395),
-           ("emission", M, 396, 440), ("ray_box fast", O, 87, 108), ("ray_box exact", O, 109, 139),
-           ("fast_atan2/ray_range", O, 140, 163), ("consider", O, 164, 190), ("plane_mask", O, 191, 204),
-           ("expand", O, 205, 268), ("open_rays/open_for", O, 72, 86), ("open_rays", O, 269, 283), ("flush_rows", O, 284, 300)]
+regions = [("staging/self/abs", M, 1, 73), ("partner rows", M, 74, 105), ("lidar setup + agents", M, 106, 153),
+           ("group list", M, 154, 200), ("band loop control", M, 201, 229), ("knn sweep", M, 230, 248),
+           ("lidar per entity", M, 249, 272), ("lidar write-out", M, 273, 303), ("select", M, 304, 399),
+           ("emission", M, 400, 445), ("best_t/ray_bits/open_for", O, 76, 89), ("ray_box fast", O, 90, 120),
+           ("ray_box exact", O, 121, 151), ("fast_atan2/ray_range", O, 152, 176), ("consider", O, 177, 202),
+           ("plane_mask", O, 203, 217), ("expand", O, 218, 277), ("open_rays", O, 278, 292), ("flush_rows", O, 293, 310)]
 ts = sum(v[0] for v in data.values()); ti = sum(v[1] for v in data.values())
 used = set()
 print(f"warp instructions per agent: {ti / agents:.0f}")
