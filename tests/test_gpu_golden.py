@@ -104,3 +104,30 @@ def test_bev_grid_bit_exact(tmp_path):
         orc.step(); eng.step()
         if t == 4:
             orc.reset([0, 2]); eng.reset([0, 2])
+
+
+def test_dense_map_overflow_paths(tmp_path):
+    """The reference's own scene at polylineReductionThreshold = 0 (9 899 road entities, 310 groups) with a
+    100 m radius: more in-radius entities than the candidate buffer holds and more groups than one list
+    pass, so the slow selection path and the multi-pass group loop are what produce the rows."""
+    from oracle.step_oracle import OracleManager
+    scenes = unpack(["womd_test_scene"], tmp_path)
+    pd = param_dict(polylineReductionThreshold=0.0, observationRadius=100.0, dynamicsModel=1, enableLidar=True,
+                    initOnlyValidAgentsAtFirstStep=False, maxNumControlledAgents=8)
+    orc = OracleManager(scenes, engine_params(pd))
+    eng = _make(scenes, pd)
+    assert int(orc.tensor("shape")[0, 1]) == 9899
+    stats = {}
+    for t in range(3):
+        a = random_actions(t, 1, 128, 1, seed=21)
+        orc.set_actions(a); eng.set_actions(a)
+        orc.step(); eng.step()
+        compare_step(kat._snapshot(orc, TENSORS_CMP), kat._snapshot(eng, TENSORS_CMP), 100.0, True,
+                     tag=f"dense step {t + 1}", stats=stats)
+    # linear algorithm on the same map: first K in road-index order
+    pd2 = dict(pd, roadObservationAlgorithm=1, enableLidar=False)
+    orc2 = OracleManager(scenes, engine_params(pd2)); eng2 = _make(scenes, pd2)
+    orc2.step(); eng2.step()
+    ko, ke = orc2.tensor("knn_index")[0], eng2.tensor("knn_index")[0]
+    for i in range(int(orc2.tensor("shape")[0, 0])):
+        assert set(ko[i][ko[i] >= 0].tolist()) == set(ke[i][ke[i] >= 0].tolist()), i
