@@ -13,11 +13,11 @@ for r in rows:
     data[k] = (v[0] + int(r[si] or 0), v[1] + int(r[ie] or 0))
 M, O = "kernels_obs_main.cuh", "kernels_obs.cuh"
 regions = [("staging/self/abs", M, 1, 73), ("partner rows", M, 74, 105), ("lidar setup + agents", M, 106, 153),
-           ("group list", M, 154, 200), ("band loop control", M, 201, 229), ("knn sweep", M, 230, 248),
-           ("lidar per entity", M, 249, 272), ("lidar write-out", M, 273, 303), ("select", M, 304, 399),
-           ("emission", M, 400, 445), ("best_t/ray_bits/open_for", O, 76, 89), ("ray_box fast", O, 90, 120),
+           ("group list", M, 154, 204), ("band loop control", M, 205, 237), ("knn sweep", M, 238, 256),
+           ("lidar per entity", M, 257, 280), ("lidar write-out", M, 281, 311), ("select", M, 312, 473),
+           ("emission", M, 474, 520), ("best_t/ray_bits/open_for", O, 76, 89), ("ray_box fast", O, 90, 120),
            ("ray_box exact", O, 121, 151), ("fast_atan2/ray_range", O, 152, 176), ("consider", O, 177, 202),
-           ("plane_mask", O, 203, 217), ("expand", O, 218, 277), ("open_rays", O, 278, 292), ("flush_rows", O, 293, 310)]
+           ("plane_mask", O, 203, 217), ("expand", O, 218, 277), ("open_rays", O, 278, 292), ("flush_rows", O, 293, 320)]
 ts = sum(v[0] for v in data.values()); ti = sum(v[1] for v in data.values())
 used = set()
 print(f"warp instructions per agent: {ti / agents:.0f}")
