@@ -106,3 +106,62 @@ def test_set_maps_and_delete_agents(synth_dir):
     assert int(sim.shape_tensor().to_torch()[1, 0]) == 61
     ref.step(); sim.step()
     compare_step(snapshot_ref(ref), snapshot_engine(sim), 50.0, False, tag="step after deleteAgents")
+
+
+def test_collision_stress_128_agents(synth_dir):
+    """config 5 shape: every one of the 128 slots live, agents packed into a double intersection, road edges
+    sampled at 0.25 m (about 4 000 edge segments), AgentStop. Collision / done / info flags bit-exact."""
+    _need()
+    import os
+    d = os.path.join(synth_dir, "stress128")
+    scenes = _scenes(d, 1, num_agents=128, stress=True, edge_spacing=0.25)
+    pd = param_dict(dynamicsModel=1, collisionBehaviour=0, maxNumControlledAgents=128,
+                    polylineReductionThreshold=0.0)
+    ref, sim, _ = run_parity(scenes, pd, 40, names=["shape", "done", "info", "steps_remaining", "controlled_state",
+                                                    "response_type", "self_observation",
+                                                    "absolute_self_observation", "reward", "partner_observations"])
+    shape = ref.tensor("shape")[0]
+    assert shape[0] == 128 and shape[1] >= 4000
+    info = ref.tensor("info")[0]
+    assert (info[:, :3].sum(1) > 0).mean() >= 0.2, "expected >= 20 % of the agents to have collided"
+
+
+def test_auto_reset_rollout_from_device_pool(synth_dir):
+    """config 4 shape: episodes end, finished worlds are re-bound to other pooled scenarios on the device
+    (gd_bind_worlds) and keep stepping; the reference does the same through set_maps. Tensors equal after
+    every re-bind and at the end."""
+    _need()
+    import os
+    import torch
+    from gpudrive_lab_b200 import madrona_gpudrive as mg
+    from helpers import (TENSORS_CMP, compare_step, engine_params, random_actions, ref_params, snapshot_engine,
+                         snapshot_ref)
+    from oracle.refmgr import RefManager
+    d = os.path.join(synth_dir, "pool")
+    pool = _scenes(d, 4, num_agents=12)
+    pd = param_dict(dynamicsModel=2, maxNumControlledAgents=12, distanceToGoalThreshold=3.0)
+    cur = [0, 1]
+    ref = RefManager([pool[i] for i in cur], ref_params(pd))
+    sim = mg.SimManager(mg.madrona.ExecMode.CUDA, 0, [pool[i] for i in cur], engine_params(pd))
+    ids = [sim.pool_add(p) for p in pool]
+    act = sim.action_tensor().to_torch()
+    stats = {}
+    for t in range(120):
+        a = random_actions(t, 2, 128, 2, seed=13)
+        ref.tensor("action")[...] = a
+        act.copy_(torch.from_numpy(a)); torch.cuda.synchronize()
+        ref.step(); sim.step()
+        if t % 10 == 9:
+            compare_step(snapshot_ref(ref), snapshot_engine(sim), 50.0, False, tag=f"step {t + 1}", stats=stats)
+        if t in (45, 91):       # world (t == 45 ? 1 : 0) switches to the next pooled scenario
+            w = 1 if t == 45 else 0
+            cur[w] = (cur[w] + 2) % 4
+            ref.set_maps([pool[i] for i in cur])              # reference: re-parses and rebuilds every world
+            ref.reset([w])
+            sim.bind_worlds([w], [ids[cur[w]]])               # engine: re-bind + reset on the device
+            # the reference's set_maps re-creates every world (fresh episodes everywhere, src/mgr.cpp:590-654);
+            # mirror that on the other world for a like-for-like state
+            sim.reset([1 - w]); ref.reset([1 - w])
+            compare_step(snapshot_ref(ref, TENSORS_CMP + ["map_observation", "expert_trajectory"]),
+                         snapshot_engine(sim, TENSORS_CMP + ["map_observation", "expert_trajectory"]),
+                         50.0, False, tag=f"after re-bind at {t + 1}", stats=stats)
