@@ -53,7 +53,7 @@ EXPORTED_SYMBOLS = [
     "gd_create", "gd_destroy", "gd_step", "gd_step_async", "gd_sync", "gd_reset", "gd_set_maps",
     "gd_delete_agents", "gd_tensor", "gd_step_host", "gd_pool_add", "gd_bind_worlds", "gd_stats",
     "gd_num_worlds", "gd_max_agents", "gd_launch_count", "gd_stream", "gd_last_error",
-    "gd_scene_info", "gd_scene_tensors", "gd_scene_road_pose", "gd_set_option", "gd_kernel_times",
+    "gd_scene_info", "gd_scene_tensors", "gd_scene_road_pose", "gd_policy_obs", "gd_set_option", "gd_kernel_times",
 ]
 
 TENSOR_IDS = {
@@ -104,6 +104,7 @@ def load():
     lib.gd_scene_info.argtypes = [C.c_char_p, C.POINTER(GdParams), C.c_int32, C.POINTER(GdSceneInfo)]
     lib.gd_scene_tensors.argtypes = [C.c_char_p, C.POINTER(GdParams), C.c_int32, C.c_void_p, C.c_int32,
                                      C.c_void_p, C.c_void_p, C.c_int32]
+    lib.gd_policy_obs.argtypes = [H, C.c_int32, C.POINTER(GdTensorDesc)]
     lib.gd_scene_road_pose.argtypes = [C.c_char_p, C.POINTER(GdParams), C.c_int32, C.c_void_p, C.c_int32]
     _lib = lib
     return lib

@@ -147,6 +147,13 @@ int gd_scene_tensors(const char *path, const GdParams *params, int32_t max_agent
     })
 }
 
+int gd_policy_obs(GdHandle h, int32_t normalize, GdTensorDesc *out) {
+    GD_TRY({
+        gd::TensorDesc d = E(h)->policyObs(normalize);
+        memcpy(out, &d, sizeof(d));
+    })
+}
+
 int gd_scene_road_pose(const char *path, const GdParams *params, int32_t max_agents, float *pose,
                        int32_t rows_cap) {
     GD_TRY({

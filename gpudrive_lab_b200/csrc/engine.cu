@@ -9,6 +9,7 @@
 
 #include "kernels_bev.cuh"
 #include "kernels_obs_main.cuh"
+#include "kernels_policy.cuh"
 #include "kernels_reset.cuh"
 #include "kernels_step.cuh"
 
@@ -526,6 +527,19 @@ void Engine::stepHost(const float *actions, int action_cols, float *reward, int3
     if (info) GD_CUDA(cudaMemcpyAsync(info, ex_.info, WS * kInfoSize * sizeof(int32_t), cudaMemcpyDeviceToHost, copy_stream_));
     GD_CUDA(cudaStreamSynchronize(copy_stream_));
     sync();
+}
+
+TensorDesc Engine::policyObs(int normalize) {
+    GD_CUDA(cudaSetDevice(gpu_));
+    const int width = kPolicyEgo + (S_ - 1) * kPolicyPartner + kMaxAgentMapObs * kPolicyRoad;
+    if (!d_policy_obs_) d_policy_obs_ = devAlloc<float>(owned_, (size_t)W_ * S_ * width);
+    k_policy_obs<<<W_ * S_, 256, 0, stream_>>>(ex_, d_policy_obs_, S_, normalize ? 1 : 0);
+    launches_++;
+    GD_CUDA(cudaGetLastError());
+    GD_CUDA(cudaStreamSynchronize(stream_));
+    TensorDesc d{};
+    d.ptr = d_policy_obs_; d.dtype = 0; d.ndim = 3; d.shape[0] = W_; d.shape[1] = S_; d.shape[2] = width; d.device = gpu_;
+    return d;
 }
 
 void Engine::setOption(int option, int value) {

@@ -123,6 +123,8 @@ public:
     int poolAdd(const std::string &path);       // returns scene id
     void bindWorlds(const int32_t *worlds, const int32_t *scene_ids, int n);   // + reset
     StepStats stats();
+    // flat normalised policy observation (GPUDriveTorchEnv.get_obs) computed from the current exports
+    TensorDesc policyObs(int normalize);
     // options: 0 = write the knn index side buffer (default 1), 1 = per-kernel CUDA-event timing (default 0)
     void setOption(int option, int value);
     // accumulated device time of the two step kernels since profiling was switched on (ms) and the step count
@@ -168,6 +170,7 @@ private:
     std::vector<void *> owned_;
     int32_t *d_worklist_ = nullptr;   // [W] scratch for reset lists
     float *h_pinned_actions_ = nullptr;
+    float *d_policy_obs_ = nullptr;       // [W,S,6 + (S-1)*6 + 200*13], allocated on first use
     float *d_act_stage_ = nullptr;        // [W*S*10] contiguous landing buffer of stepHost's actions
     cudaStream_t copy_stream_ = nullptr;  // stepHost: reward / done / info leave while k_obs still runs
     cudaEvent_t ev_agents_ = nullptr, ev_copied_ = nullptr;

@@ -224,6 +224,13 @@ class SimManager:
         _capi.check(self._lib.gd_kernel_times(self._h, C.byref(a), C.byref(o), C.byref(n)))
         return {"k_agents_ms": a.value, "k_obs_ms": o.value, "steps": n.value}
 
+    def policy_observation_tensor(self, normalize=True) -> Tensor:
+        """Flat policy observation [W, S, 6 + (S-1)*6 + 200*13] (GPUDriveTorchEnv.get_obs defaults), computed on
+        the device from the current exports; recomputed at every call."""
+        d = _capi.GdTensorDesc()
+        _capi.check(self._lib.gd_policy_obs(self._h, 1 if normalize else 0, C.byref(d)))
+        return Tensor(d, self)
+
     def launch_count(self) -> int:
         return int(self._lib.gd_launch_count(self._h))
 

@@ -126,6 +126,11 @@ int gd_tensor(GdHandle h, int32_t tensor_id, GdTensorDesc *out);
  * (gpudrive/env/env_torch.py:606-660). */
 int gd_step_host(GdHandle h, const float *actions, int32_t action_cols, float *reward, int32_t *done,
                  int32_t *info);
+/* Flat policy observation of every agent slot, computed on the device from the current exports in one pass:
+ * what GPUDriveTorchEnv.get_obs() builds in Python with the default ego_state + partner_obs + road_map_obs
+ * (gpudrive/env/env_torch.py:756-891,1172-1216; normalisation constants gpudrive/env/constants.py).
+ * out: f32 [W, S, 6 + (S-1)*6 + 200*13], valid until the next call. normalize = config.norm_obs. */
+int gd_policy_obs(GdHandle h, int32_t normalize, GdTensorDesc *out);
 /* Device scenario pool: load a scenario once, re-bind worlds to pooled scenarios + reset them. */
 int gd_pool_add(GdHandle h, const char *scene_path, int32_t *scene_id_out);
 int gd_bind_worlds(GdHandle h, const int32_t *worlds, const int32_t *scene_ids, int32_t n);

@@ -92,3 +92,32 @@ def test_errors_are_reported_not_fatal(tmp_path):
     with pytest.raises(RuntimeError):
         sim.reset([5])
     sim.step()                                        # the handle is still usable
+
+
+def test_policy_observation_matches_reference_python(tmp_path):
+    """gd_policy_obs on the golden input tensors is bit-identical to the output of the
+    reference's own Python post-processing, and on live engine tensors to its numpy restatement."""
+    import os
+    import torch
+    from golden_util import GOLDEN
+    from policy_obs_ref import policy_obs
+    g = np.load(os.path.join(GOLDEN, "policy_obs.npz"))
+    scenes = unpack(["synth_a", "synth_b"], tmp_path)
+    sim = _sim(scenes, param_dict(dynamicsModel=2, maxNumControlledAgents=12))
+    A = g["self_observation"].shape[1]
+    so, po, rm = (sim.self_observation_tensor().to_torch(), sim.partner_observations_tensor().to_torch(),
+                  sim.agent_roadmap_tensor().to_torch())
+    so[:, :A].copy_(torch.from_numpy(g["self_observation"]))
+    po[:, :A].copy_(torch.from_numpy(g["partner_observations"]))
+    rm[:, :A].copy_(torch.from_numpy(g["agent_roadmap"]))
+    torch.cuda.synchronize()
+    for norm, key in ((True, "obs_norm"), (False, "obs_raw")):
+        out = sim.policy_observation_tensor(normalize=norm).to_torch().cpu().numpy()
+        assert out.shape == (2, 128, 3368)
+        assert np.array_equal(out[:, :A].view(np.uint32), g[key].view(np.uint32)), key
+    # live tensors after a few steps, every slot (padding slots included, like the Python path)
+    for _ in range(3):
+        sim.step()
+    out = sim.policy_observation_tensor().to_torch().cpu().numpy()
+    exp = policy_obs(so.cpu().numpy(), po.cpu().numpy(), rm.cpu().numpy(), True)
+    assert np.array_equal(out.view(np.uint32), exp.view(np.uint32))
