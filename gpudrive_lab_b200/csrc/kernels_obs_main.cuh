@@ -119,7 +119,10 @@ k_obs(const SceneDev *__restrict__ scenes, StateDev st, Exports ex, Params prm, 
         for (int i = lane; i < NRAY; i += 32) {
             const float theta = __fadd_rn(__fmul_rn(kLidarAngle,
                 __fsub_rn(__fdiv_rn(2.f * (float)i, (float)NRAY), 1.f)), head);
-            const float x = cos_hp(theta), y = sin_hp(theta);      // sim.cpp:411-412
+            // sim.cpp:411-412. Observation output with a 1e-5 bar, not agent state: CUDA's sincosf (<= 2 ulp
+            // from glibc's cosf / sinf) instead of the bit-exact restatement, which costs four times as much.
+            float x, y;
+            sincosf(theta, &y, &x);
             const float dx = __fadd_rn(__fmul_rn(x, rgx), __fmul_rn(y, fwx));
             const float dy = __fadd_rn(__fmul_rn(x, rgy), __fmul_rn(y, fwy));
             const float inv = __fdiv_rn(1.f, __fsqrt_rn(__fadd_rn(len2_xy(dx, dy), 0.f)));
@@ -130,8 +133,11 @@ k_obs(const SceneDev *__restrict__ scenes, StateDev st, Exports ex, Params prm, 
         const float delta = (2.f * kLidarAngle) / (float)NRAY;
         const float mid = yaw + head - kLidarAngle + 0.5f * (float)(NRAY - 1) * delta;
         sincosf(mid, &lc.fs, &lc.fc);
-        for (int c = 0; c < sc.numZClasses; c++)
-            zmask_classes |= plane_mask(pz, sc.zc_z[c], sc.zc_d2[c], -1.f, 1.f) << (3 * c);
+        {   // one lane per z-class, combined with a warp OR
+            int mine = 0;
+            if (lane < sc.numZClasses) mine = plane_mask(pz, sc.zc_z[lane], sc.zc_d2[lane], -1.f, 1.f) << (3 * lane);
+            zmask_classes = (int)__reduce_or_sync(FULL, (unsigned)mine);
+        }
         __syncwarp();
         // other agents first: few boxes, and their hits close rays before the road groups are visited
         for (int base = 0; base < A; base += 32) {
@@ -157,7 +163,6 @@ k_obs(const SceneDev *__restrict__ scenes, StateDev st, Exports ex, Params prm, 
     const bool first_k_only = prm.roadObservationAlgorithm == RO_AllEntities;
     const float rpad = radius * 1.00001f + 1e-3f;      // |dx|,|dy| beyond this cannot be in radius
     const int G = sc.numGroups;
-    const int nZ = sc.numZClasses;
     for (int g0 = 0; g0 < G && (want_cands || lidar_on); g0 += OBS_GCAP) {
         // ---- one lane per group: can its bounding circle matter to this agent?
         const int gN = min(OBS_GCAP, G - g0);
@@ -175,9 +180,8 @@ k_obs(const SceneDev *__restrict__ scenes, StateDev st, Exports ex, Params prm, 
                 const bool nearg = want_cands && dmin <= rpad;
                 int pmg = 0, lo = 0, hi = NRAY - 1;
                 if (lidar_on && dmin <= kLidarDistance) {
-                    const unsigned cm = __float_as_uint(gc.w);
-                    for (int c = 0; c < nZ; c++)
-                        if ((cm >> c) & 1u) pmg |= (zmask_classes >> (3 * c)) & 7;
+                    for (unsigned cm = __float_as_uint(gc.w) & 0xffu; cm; cm &= cm - 1)      // usually one class
+                        pmg |= (zmask_classes >> (3 * (__ffs(cm) - 1))) & 7;
                     if (pmg && d > gc.z * 1.0001f + 0.01f) {
                         const float s = gc.z / d;                                   // sin of the half width
                         const float w = s * rsqrtf(fmaxf(1.f - s * s, 1e-6f));      // tan >= the angle itself
