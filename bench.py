@@ -37,11 +37,14 @@ LIDAR = 50
 
 def params_dict():
     # config 3 of BASELINE.json; collision behaviour / road algorithm as SURVEY.md 8(d) config 2-3
+    # GD_BENCH_NO_LIDAR / GD_BENCH_NO_CLASSIC: kernel experiments only (time split of k_obs); the bench line
+    # is only valid without them
     return dict(polylineReductionThreshold=0.1, observationRadius=50.0, rewardType=1,
                 distanceToGoalThreshold=2.0, distanceToExpertThreshold=0.0, collisionBehaviour=2,
                 maxNumControlledAgents=AGENTS, IgnoreNonVehicles=False, roadObservationAlgorithm=0,
-                initOnlyValidAgentsAtFirstStep=True, isStaticAgentControlled=True, enableLidar=True,
-                disableClassicalObs=False, dynamicsModel=2, readFromTracksToPredict=False)
+                initOnlyValidAgentsAtFirstStep=True, isStaticAgentControlled=True,
+                enableLidar=not os.environ.get("GD_BENCH_NO_LIDAR"),
+                disableClassicalObs=bool(os.environ.get("GD_BENCH_NO_CLASSIC")), dynamicsModel=2, readFromTracksToPredict=False)
 
 
 def algorithmic_bytes(S, R, A, lidar=True):

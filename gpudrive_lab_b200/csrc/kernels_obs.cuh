@@ -25,12 +25,15 @@ namespace gd {
 
 #ifdef GD_COUNTERS     // kernel experiments only: work counters read back through gd_debug_counters
 __device__ unsigned long long g_obs_cnt[16];
-#define GD_CNT(i, v) do { if (lane == 0) atomicAdd(&g_obs_cnt[i], (unsigned long long)(v)); } while (0)
+#define GD_CNT(i, v) do { const unsigned long long cv_ = (unsigned long long)(v); if (lane == 0) atomicAdd(&g_obs_cnt[i], cv_); } while (0)
 #else
 #define GD_CNT(i, v) do { } while (0)
 #endif
 
-constexpr int OBS_WARPS = 8;              // agents per CTA
+#ifndef GD_OBS_WARPS
+#define GD_OBS_WARPS 8
+#endif
+constexpr int OBS_WARPS = GD_OBS_WARPS;   // agents per CTA
 constexpr int OBS_BLOCK = OBS_WARPS * 32;
 constexpr int OBS_CAND = 512;             // in-radius candidates kept per agent before the slow path
 constexpr int OBS_GCAP = 128;             // group descriptors per pass (4 per lane; larger maps take several passes)

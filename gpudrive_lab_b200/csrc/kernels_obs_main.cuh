@@ -150,7 +150,8 @@ k_obs(const SceneDev *__restrict__ scenes, StateDev st, Exports ex, Params prm, 
                 relx = o0.x - px; rely = o0.y - py; d0 = gb.x; d1 = gb.y;
                 cphi = 1.f - 2.f * o0.w * o0.w; sphi = 2.f * o0.z * o0.w;
                 int hi;
-                if (pm && lidar_consider(lc, relx, rely, cphi, sphi, d0, d1, lo, hi)) n = hi - lo + 1;
+                // the agent's own hull is skipped: the origin is its centre, so every face is a back face -> miss
+                if (pm && j != a && lidar_consider(lc, relx, rely, cphi, sphi, d0, d1, lo, hi)) n = hi - lo + 1;
             }
             lidar_expand(wp, lane, lo, n, pm, 0x4000u | (unsigned)j, relx, rely, cphi, sphi, d0, d1);
         }
