@@ -91,6 +91,8 @@ def load():
     lib.gd_step_host.argtypes = [H, C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p]
     lib.gd_pool_add.argtypes = [H, C.c_char_p, C.POINTER(C.c_int32)]
     lib.gd_bind_worlds.argtypes = [H, C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.c_int32]
+    lib.gd_pool_convert.argtypes = [C.POINTER(C.c_char_p), C.c_int32, C.c_float, C.c_char_p, C.c_int32]
+    lib.gd_pool_count.argtypes = [C.c_char_p, C.POINTER(C.c_int32), C.POINTER(C.c_float)]
     lib.gd_stats.argtypes = [H, C.POINTER(GdStats)]
     lib.gd_set_option.argtypes = [H, C.c_int32, C.c_int32]
     lib.gd_kernel_times.argtypes = [H, C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(C.c_int64)]

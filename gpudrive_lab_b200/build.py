@@ -16,7 +16,7 @@ HEADERS = ["engine.h", "gd_types.h", "scenario.h", "json_min.h", "glibc_trig.h",
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
     # bit-parity with the reference's CPU build: no FMA contraction on either side
-    "--fmad=false", "-Xcompiler", "-fPIC,-ffp-contract=off,-Wall,-Wno-stringop-truncation",
+    "--fmad=false", "-Xcompiler", "-fPIC,-ffp-contract=off,-Wall,-Wno-stringop-truncation,-pthread",
     "-shared",
 ]
 

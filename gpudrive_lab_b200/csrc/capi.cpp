@@ -89,6 +89,18 @@ int gd_bind_worlds(GdHandle h, const int32_t *worlds, const int32_t *scene_ids, 
     GD_TRY({ E(h)->bindWorlds(worlds, scene_ids, n); })
 }
 
+int gd_pool_convert(const char *const *json_paths, int32_t n, float threshold, const char *out_path, int32_t threads) {
+    GD_TRY({
+        std::vector<std::string> paths;
+        for (int32_t i = 0; i < n; i++) paths.emplace_back(json_paths[i]);
+        gd::writeScenarioPool(out_path, paths, threshold, threads);
+    })
+}
+
+int gd_pool_count(const char *pool_path, int32_t *count_out, float *threshold_out) {
+    GD_TRY({ *count_out = gd::scenarioPoolCount(pool_path, threshold_out); })
+}
+
 int gd_stats(GdHandle h, GdStats *out) {
     GD_TRY({
         gd::StepStats s = E(h)->stats();
@@ -109,7 +121,7 @@ const char *gd_last_error(void) { return g_last_error.c_str(); }
 int gd_scene_info(const char *path, const GdParams *params, int32_t max_agents, GdSceneInfo *out) {
     GD_TRY({
         gd::Params p = toParams(params);
-        gd::ParsedMap m = gd::parseMapFile(path, p.polylineReductionThreshold);
+        gd::ParsedMap m = gd::loadParsedMap(path, p.polylineReductionThreshold);
         gd::SceneData s = gd::buildScene(m, p, max_agents, nullptr, 0);
         out->num_agents = s.numAgents;
         out->num_roads = s.numRoads;
@@ -122,7 +134,7 @@ int gd_scene_tensors(const char *path, const GdParams *params, int32_t max_agent
                      int32_t map_rows_cap, float *traj, float *agent_static, int32_t agent_cap) {
     GD_TRY({
         gd::Params p = toParams(params);
-        gd::ParsedMap m = gd::parseMapFile(path, p.polylineReductionThreshold);
+        gd::ParsedMap m = gd::loadParsedMap(path, p.polylineReductionThreshold);
         gd::SceneData s = gd::buildScene(m, p, max_agents, nullptr, 0);
         if (map_obs) {
             for (int r = 0; r < s.numRoads && r < map_rows_cap; r++) {
@@ -158,7 +170,7 @@ int gd_scene_road_pose(const char *path, const GdParams *params, int32_t max_age
                        int32_t rows_cap) {
     GD_TRY({
         gd::Params p = toParams(params);
-        gd::ParsedMap m = gd::parseMapFile(path, p.polylineReductionThreshold);
+        gd::ParsedMap m = gd::loadParsedMap(path, p.polylineReductionThreshold);
         gd::SceneData s = gd::buildScene(m, p, max_agents, nullptr, 0);
         for (int r = 0; r < s.numRoads && r < rows_cap; r++) {
             float *row = pose + (size_t)r * 4;

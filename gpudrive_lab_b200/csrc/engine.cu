@@ -344,7 +344,7 @@ int Engine::sceneFor(const std::string &path, const std::vector<int32_t> &delete
     auto pit = parsed_cache_.find(path);
     if (pit != parsed_cache_.end()) pm = pit->second;
     else {
-        pm = std::make_shared<ParsedMap>(parseMapFile(path, params_.polylineReductionThreshold));
+        pm = std::make_shared<ParsedMap>(loadParsedMap(path, params_.polylineReductionThreshold));
         if (parsed_cache_.size() < 64) parsed_cache_[path] = pm;   // small LRU-less cache for deleteAgents
     }
     SceneData s = buildScene(*pm, params_, S_, deleted.data(), (int)deleted.size());

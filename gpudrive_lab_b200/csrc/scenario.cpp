@@ -3,6 +3,7 @@
 #include "scenario.h"
 
 #include <algorithm>
+#include <atomic>
 #include <cerrno>
 #include <cmath>
 #include <cstdio>
@@ -10,6 +11,7 @@
 #include <fstream>
 #include <sstream>
 #include <stdexcept>
+#include <thread>
 #include <unordered_map>
 #include <unordered_set>
 
@@ -290,6 +292,177 @@ ParsedMap parseMapFile(const std::string &path, float threshold) {
     } catch (const std::exception &e) {
         throw std::runtime_error(path + ": " + e.what());
     }
+}
+
+// ---------------------------------------------------------------------------------------------
+// Binary scenario pool
+//   header : "GDPOOL1\0" | float threshold | uint32 count | uint64 offset[count + 1]
+//   entry  : mapName[32] scenarioId[32] mean(2 f32) numRoadSegments(u32)
+//            numObjects(u32) objects... numRoads(u32) roads...   (field by field, little endian, no padding)
+// ---------------------------------------------------------------------------------------------
+namespace {
+
+const char kPoolMagic[8] = {'G', 'D', 'P', 'O', 'O', 'L', '1', '\0'};
+
+struct BlobWriter {
+    std::string out;
+    void raw(const void *p, size_t n) { out.append(static_cast<const char *>(p), n); }
+    template <typename T> void put(const T &v) { raw(&v, sizeof(T)); }
+};
+
+struct BlobReader {
+    const char *p, *end;
+    void raw(void *dst, size_t n) {
+        if ((size_t)(end - p) < n) throw std::runtime_error("scenario pool entry is truncated");
+        memcpy(dst, p, n); p += n;
+    }
+    template <typename T> T get() { T v; raw(&v, sizeof(T)); return v; }
+};
+
+std::string encodeMap(const ParsedMap &m) {
+    BlobWriter w;
+    w.raw(m.mapName, 32); w.raw(m.scenarioId, 32);
+    w.put(m.mean.x); w.put(m.mean.y); w.put(m.numRoadSegments);
+    w.put((uint32_t)m.objects.size());
+    for (const ParsedObject &o : m.objects) {
+        w.raw(o.position, sizeof(o.position)); w.put(o.length); w.put(o.width); w.put(o.height);
+        w.raw(o.heading, sizeof(o.heading)); w.raw(o.velocity, sizeof(o.velocity));
+        for (int i = 0; i < MAX_POSITIONS; i++) w.put((uint8_t)(o.valid[i] ? 1 : 0));
+        w.put(o.goal.x); w.put(o.goal.y); w.put(o.type); w.raw(o.meta, sizeof(o.meta));
+        w.put(o.numPositions); w.put(o.numHeadings); w.put(o.numVelocities); w.put(o.numValid);
+        w.put(o.id); w.put((uint8_t)(o.markAsExpert ? 1 : 0));
+    }
+    w.put((uint32_t)m.roads.size());
+    for (const ParsedRoad &r : m.roads) {
+        w.put(r.id); w.put(r.mapType); w.put(r.type); w.put(r.numPoints);
+        w.put((uint32_t)r.geometry.size());
+        if (!r.geometry.empty()) w.raw(r.geometry.data(), sizeof(Vec2) * r.geometry.size());
+    }
+    return std::move(w.out);
+}
+
+ParsedMap decodeMap(const char *begin, const char *end) {
+    BlobReader r{begin, end};
+    ParsedMap m;
+    r.raw(m.mapName, 32); r.raw(m.scenarioId, 32);
+    m.mean.x = r.get<float>(); m.mean.y = r.get<float>(); m.numRoadSegments = r.get<uint32_t>();
+    const uint32_t nobj = r.get<uint32_t>();
+    if (nobj > (uint32_t)MAX_OBJECTS) throw std::runtime_error("scenario pool entry: object count out of range");
+    m.objects.resize(nobj);
+    for (ParsedObject &o : m.objects) {
+        r.raw(o.position, sizeof(o.position)); o.length = r.get<float>(); o.width = r.get<float>(); o.height = r.get<float>();
+        r.raw(o.heading, sizeof(o.heading)); r.raw(o.velocity, sizeof(o.velocity));
+        for (int i = 0; i < MAX_POSITIONS; i++) o.valid[i] = r.get<uint8_t>() != 0;
+        o.goal.x = r.get<float>(); o.goal.y = r.get<float>(); o.type = r.get<int32_t>(); r.raw(o.meta, sizeof(o.meta));
+        o.numPositions = r.get<uint32_t>(); o.numHeadings = r.get<uint32_t>(); o.numVelocities = r.get<uint32_t>();
+        o.numValid = r.get<uint32_t>(); o.id = r.get<uint32_t>(); o.markAsExpert = r.get<uint8_t>() != 0;
+    }
+    const uint32_t nroad = r.get<uint32_t>();
+    if (nroad > (uint32_t)MAX_ROADS) throw std::runtime_error("scenario pool entry: road count out of range");
+    m.roads.resize(nroad);
+    for (ParsedRoad &rd : m.roads) {
+        rd.id = r.get<uint32_t>(); rd.mapType = r.get<int32_t>(); rd.type = r.get<int32_t>(); rd.numPoints = r.get<uint32_t>();
+        const uint32_t ng = r.get<uint32_t>();
+        if (ng > (uint32_t)MAX_GEOMETRY) throw std::runtime_error("scenario pool entry: geometry count out of range");
+        rd.geometry.resize(ng);
+        if (ng) r.raw(rd.geometry.data(), sizeof(Vec2) * ng);
+    }
+    return m;
+}
+
+struct PoolHeader { float threshold; uint32_t count; std::vector<uint64_t> offsets; };
+
+PoolHeader readPoolHeader(std::ifstream &in, const std::string &path) {
+    char magic[8];
+    PoolHeader h;
+    in.read(magic, 8);
+    if (!in || memcmp(magic, kPoolMagic, 8) != 0) throw std::runtime_error(path + ": not a scenario pool file");
+    in.read(reinterpret_cast<char *>(&h.threshold), 4);
+    in.read(reinterpret_cast<char *>(&h.count), 4);
+    if (!in || h.count > (1u << 24)) throw std::runtime_error(path + ": bad scenario pool header");
+    h.offsets.resize((size_t)h.count + 1);
+    in.read(reinterpret_cast<char *>(h.offsets.data()), sizeof(uint64_t) * h.offsets.size());
+    if (!in) throw std::runtime_error(path + ": truncated scenario pool header");
+    return h;
+}
+
+// "<file>#<index>" with a non-empty all-digit index
+bool splitPoolRef(const std::string &path, std::string *file, int *index) {
+    const size_t k = path.rfind('#');
+    if (k == std::string::npos || k + 1 >= path.size() || path.size() - k > 9) return false;
+    int v = 0;
+    for (size_t i = k + 1; i < path.size(); i++) {
+        if (path[i] < '0' || path[i] > '9') return false;
+        v = v * 10 + (path[i] - '0');
+    }
+    *file = path.substr(0, k); *index = v;
+    return true;
+}
+
+} // namespace
+
+void writeScenarioPool(const std::string &out_path, const std::vector<std::string> &json_paths, float threshold,
+                       int threads) {
+    const size_t n = json_paths.size();
+    std::vector<std::string> blobs(n), errors(n);
+    std::atomic<size_t> next{0};
+    auto work = [&]() {
+        for (size_t i = next.fetch_add(1); i < n; i = next.fetch_add(1)) {
+            try { blobs[i] = encodeMap(loadParsedMap(json_paths[i], threshold)); }
+            catch (const std::exception &e) { errors[i] = e.what(); }
+        }
+    };
+    const int T = std::max(1, std::min<int>(threads > 0 ? threads : (int)std::thread::hardware_concurrency(), (int)std::max<size_t>(n, 1)));
+    std::vector<std::thread> pool;
+    for (int t = 1; t < T; t++) pool.emplace_back(work);
+    work();
+    for (auto &t : pool) t.join();
+    for (size_t i = 0; i < n; i++) if (!errors[i].empty()) throw std::runtime_error(errors[i]);
+    std::ofstream out(out_path, std::ios::binary | std::ios::trunc);
+    if (!out.is_open()) throw std::runtime_error("cannot write scenario pool: " + out_path);
+    const uint32_t count = (uint32_t)n;
+    std::vector<uint64_t> offsets(n + 1);
+    uint64_t off = 8 + 4 + 4 + sizeof(uint64_t) * (n + 1);
+    for (size_t i = 0; i < n; i++) { offsets[i] = off; off += blobs[i].size(); }
+    offsets[n] = off;
+    out.write(kPoolMagic, 8);
+    out.write(reinterpret_cast<const char *>(&threshold), 4);
+    out.write(reinterpret_cast<const char *>(&count), 4);
+    out.write(reinterpret_cast<const char *>(offsets.data()), sizeof(uint64_t) * offsets.size());
+    for (const std::string &b : blobs) out.write(b.data(), (std::streamsize)b.size());
+    if (!out) throw std::runtime_error("short write on scenario pool: " + out_path);
+}
+
+int scenarioPoolCount(const std::string &pool_path, float *threshold_out) {
+    std::ifstream in(pool_path, std::ios::binary);
+    if (!in.is_open()) throw std::runtime_error("cannot open scenario pool: " + pool_path);
+    PoolHeader h = readPoolHeader(in, pool_path);
+    if (threshold_out) *threshold_out = h.threshold;
+    return (int)h.count;
+}
+
+ParsedMap readScenarioPoolEntry(const std::string &pool_path, int index, float threshold) {
+    std::ifstream in(pool_path, std::ios::binary);
+    if (!in.is_open()) throw std::runtime_error("cannot open scenario pool: " + pool_path);
+    PoolHeader h = readPoolHeader(in, pool_path);
+    if (index < 0 || (uint32_t)index >= h.count)
+        throw std::runtime_error(pool_path + ": entry " + std::to_string(index) + " of " + std::to_string(h.count) + " does not exist");
+    if (memcmp(&h.threshold, &threshold, 4) != 0)
+        throw std::runtime_error(pool_path + ": built with polylineReductionThreshold " + std::to_string(h.threshold) +
+                                 ", asked for " + std::to_string(threshold));
+    const uint64_t a = h.offsets[index], b = h.offsets[index + 1];
+    if (b < a || b - a > (1ull << 31)) throw std::runtime_error(pool_path + ": corrupt entry table");
+    std::string blob((size_t)(b - a), '\0');
+    in.seekg((std::streamoff)a);
+    in.read(&blob[0], (std::streamsize)blob.size());
+    if (!in) throw std::runtime_error(pool_path + ": truncated entry " + std::to_string(index));
+    return decodeMap(blob.data(), blob.data() + blob.size());
+}
+
+ParsedMap loadParsedMap(const std::string &path, float threshold) {
+    std::string file; int index = 0;
+    if (splitPoolRef(path, &file, &index)) return readScenarioPoolEntry(file, index, threshold);
+    return parseMapFile(path, threshold);
 }
 
 // ---------------------------------------------------------------------------------------------

@@ -81,6 +81,18 @@ struct SceneData {
 ParsedMap parseMapFile(const std::string &path, float polylineReductionThreshold);
 ParsedMap parseMapString(const char *begin, const char *end, float polylineReductionThreshold);
 
+// Binary scenario pool: the ParsedMaps of many scenarios in one file, so that a pool is
+// parsed from JSON once (in parallel) and afterwards read back at memory speed. The file depends on the
+// polyline reduction threshold only (it is applied while parsing, MapReader / json_serialization.hpp:160-240);
+// every other parameter still acts in buildScene. A scene path of the form "<file>#<index>" names entry
+// <index> of pool <file> wherever a JSON path is accepted.
+void writeScenarioPool(const std::string &out_path, const std::vector<std::string> &json_paths, float threshold,
+                       int threads);
+int scenarioPoolCount(const std::string &pool_path, float *threshold_out);
+ParsedMap readScenarioPoolEntry(const std::string &pool_path, int index, float threshold);
+// JSON file or pool reference
+ParsedMap loadParsedMap(const std::string &path, float threshold);
+
 // deleted: agent ids excluded from creation (DeletedAgents singleton), may be null.
 SceneData buildScene(const ParsedMap &map, const Params &params, int max_agents,
                      const int32_t *deleted, int num_deleted);

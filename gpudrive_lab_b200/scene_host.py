@@ -36,3 +36,20 @@ def scene_tensors(path: str, params, max_agents: int = 128) -> dict:
     _capi.check(lib.gd_scene_road_pose(str(path).encode(), C.byref(p), max_agents, pose.ctypes.data, R))
     info.update(map_obs=map_obs[:R], traj=traj[:A], agent_static=stat[:A], road_pose=pose[:R])
     return info
+
+
+def convert_pool(json_paths, out_path: str, polyline_reduction_threshold: float, threads: int = 0) -> list[str]:
+    """Parse JSON scenarios once, in parallel, into one binary scenario-pool file (gd_pool_convert).
+    Returns the scene references ("<out_path>#<i>") that every scene-path argument accepts afterwards."""
+    lib = _capi.load()
+    arr = (C.c_char_p * len(json_paths))(*[str(p).encode() for p in json_paths])
+    _capi.check(lib.gd_pool_convert(arr, len(json_paths), float(polyline_reduction_threshold), str(out_path).encode(), threads))
+    return [f"{out_path}#{i}" for i in range(len(json_paths))]
+
+
+def pool_scenes(pool_path: str) -> list[str]:
+    """Scene references of an existing pool file."""
+    lib = _capi.load()
+    n, thr = C.c_int32(0), C.c_float(0)
+    _capi.check(lib.gd_pool_count(str(pool_path).encode(), C.byref(n), C.byref(thr)))
+    return [f"{pool_path}#{i}" for i in range(n.value)]

@@ -134,6 +134,14 @@ int gd_policy_obs(GdHandle h, int32_t normalize, GdTensorDesc *out);
 /* Device scenario pool: load a scenario once, re-bind worlds to pooled scenarios + reset them. */
 int gd_pool_add(GdHandle h, const char *scene_path, int32_t *scene_id_out);
 int gd_bind_worlds(GdHandle h, const int32_t *worlds, const int32_t *scene_ids, int32_t n);
+/* Scenario pool files (replaces the per-world MapReader JSON parse of Manager::Impl::init /
+ * setMaps, src/mgr.cpp:399-470,590-654, for pools that are loaded again and again). gd_pool_convert parses
+ * n JSON scenarios on `threads` host threads (<= 0: all cores) and writes them into one binary file; the file
+ * depends on polylineReductionThreshold only. Afterwards "<pool file>#<index>" is accepted wherever a
+ * scenario path is (gd_create, gd_set_maps, gd_pool_add, gd_scene_*) and yields bit-identical tensors. */
+int gd_pool_convert(const char *const *json_paths, int32_t n, float polylineReductionThreshold,
+                    const char *out_path, int32_t threads);
+int gd_pool_count(const char *pool_path, int32_t *count_out, float *threshold_out);
 int gd_stats(GdHandle h, GdStats *out);
 /* Engine options (no reference equivalent): GD_OPT_KNN_INDEX (default 1) writes the GD_T_KNN_INDEX side
  * buffer; GD_OPT_PROFILE (default 0) brackets the two step kernels with CUDA events on the engine stream. */

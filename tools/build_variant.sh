@@ -6,5 +6,5 @@ name=$1; shift
 root=$(cd "$(dirname "$0")/.." && pwd)
 mkdir -p "$root/variants"
 cd "$root/gpudrive_lab_b200/csrc"
-nvcc -gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -std=c++17 --fmad=false -Xcompiler -fPIC,-ffp-contract=off -shared "$@" -o "$root/variants/lib_$name.so" engine.cu scenario.cpp capi.cpp 2>&1 | grep -v "warning\|^ *$\|\^\|Remark\|const int A" || true
+nvcc -gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -std=c++17 --fmad=false -Xcompiler -fPIC,-ffp-contract=off,-pthread -shared "$@" -o "$root/variants/lib_$name.so" engine.cu scenario.cpp capi.cpp 2>&1 | grep -v "warning\|^ *$\|\^\|Remark\|const int A" || true
 ls -la "$root/variants/lib_$name.so"
