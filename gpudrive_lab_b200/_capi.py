@@ -54,6 +54,7 @@ EXPORTED_SYMBOLS = [
     "gd_delete_agents", "gd_tensor", "gd_step_host", "gd_pool_add", "gd_bind_worlds", "gd_stats",
     "gd_num_worlds", "gd_max_agents", "gd_launch_count", "gd_stream", "gd_last_error",
     "gd_scene_info", "gd_scene_tensors", "gd_scene_road_pose", "gd_policy_obs", "gd_set_option", "gd_kernel_times",
+    "gd_pool_convert", "gd_pool_count",
 ]
 
 TENSOR_IDS = {
