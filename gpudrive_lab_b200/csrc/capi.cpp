@@ -89,6 +89,22 @@ int gd_bind_worlds(GdHandle h, const int32_t *worlds, const int32_t *scene_ids, 
     GD_TRY({ E(h)->bindWorlds(worlds, scene_ids, n); })
 }
 
+int gd_shaped_reward(GdHandle h, const GdRewardShaping *cfg, GdTensorDesc *out) {
+    GD_TRY({
+        gd::TensorDesc d = E(h)->shapedReward(cfg->mode, cfg->collision_weight, cfg->goal_achieved_weight,
+                                              cfg->off_road_weight, cfg->log_distance_weight, cfg->agent_weights,
+                                              cfg->world_time_steps);
+        memcpy(out, &d, sizeof(d));
+    })
+}
+
+int gd_expert_actions(GdHandle h, GdTensorDesc *out) {
+    GD_TRY({
+        gd::TensorDesc d = E(h)->expertActions();
+        memcpy(out, &d, sizeof(d));
+    })
+}
+
 int gd_pool_convert(const char *const *json_paths, int32_t n, float threshold, const char *out_path, int32_t threads) {
     GD_TRY({
         std::vector<std::string> paths;

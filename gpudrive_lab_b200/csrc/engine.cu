@@ -8,6 +8,7 @@
 #include <stdexcept>
 
 #include "kernels_bev.cuh"
+#include "kernels_env.cuh"
 #include "kernels_obs_main.cuh"
 #include "kernels_policy.cuh"
 #include "kernels_reset.cuh"
@@ -539,6 +540,38 @@ TensorDesc Engine::policyObs(int normalize) {
     GD_CUDA(cudaStreamSynchronize(stream_));
     TensorDesc d{};
     d.ptr = d_policy_obs_; d.dtype = 0; d.ndim = 3; d.shape[0] = W_; d.shape[1] = S_; d.shape[2] = width; d.device = gpu_;
+    return d;
+}
+
+TensorDesc Engine::shapedReward(int mode, float collision_w, float goal_w, float off_road_w, float log_dist_w,
+                                const float *agent_weights, const int32_t *world_time_steps) {
+    GD_CUDA(cudaSetDevice(gpu_));
+    if (mode < RS_Sparse || mode > RS_DistanceToLogs) throw std::runtime_error("unknown reward shaping mode");
+    if (mode == RS_Conditioned && !agent_weights) throw std::runtime_error("reward_conditioned needs the [W,S,3] weight tensor");
+    if (!d_shaped_reward_) d_shaped_reward_ = devAlloc<float>(owned_, (size_t)W_ * S_);
+    RewardShapingArgs a{mode, collision_w, goal_w, off_road_w, log_dist_w, agent_weights, world_time_steps};
+    const int n = W_ * S_;
+    k_shaped_reward<<<(n + 255) / 256, 256, 0, stream_>>>(ex_, a, d_shaped_reward_, W_, S_);
+    launches_++;
+    GD_CUDA(cudaGetLastError());
+    GD_CUDA(cudaStreamSynchronize(stream_));
+    TensorDesc d{};
+    d.ptr = d_shaped_reward_; d.dtype = 0; d.ndim = 2; d.shape[0] = W_; d.shape[1] = S_; d.device = gpu_;
+    return d;
+}
+
+TensorDesc Engine::expertActions() {
+    GD_CUDA(cudaSetDevice(gpu_));
+    const int cols = params_.dynamicsModel == DM_State ? 10 : 3;
+    const size_t n = (size_t)W_ * S_ * kTrajLen;
+    if (!d_expert_actions_) d_expert_actions_ = devAlloc<float>(owned_, n * cols);
+    k_expert_actions<<<(unsigned)((n + 255) / 256), 256, 0, stream_>>>(ex_, d_expert_actions_, n, params_.dynamicsModel);
+    launches_++;
+    GD_CUDA(cudaGetLastError());
+    GD_CUDA(cudaStreamSynchronize(stream_));
+    TensorDesc d{};
+    d.ptr = d_expert_actions_; d.dtype = 0; d.ndim = 4; d.shape[0] = W_; d.shape[1] = S_; d.shape[2] = kTrajLen;
+    d.shape[3] = cols; d.device = gpu_;
     return d;
 }
 

@@ -125,6 +125,10 @@ public:
     StepStats stats();
     // flat normalised policy observation (GPUDriveTorchEnv.get_obs) computed from the current exports
     TensorDesc policyObs(int normalize);
+    // env post-processing on the device (kernels_env.cuh)
+    TensorDesc shapedReward(int mode, float collision_w, float goal_w, float off_road_w, float log_dist_w,
+                            const float *agent_weights, const int32_t *world_time_steps);
+    TensorDesc expertActions();
     // options: 0 = write the knn index side buffer (default 1), 1 = per-kernel CUDA-event timing (default 0)
     void setOption(int option, int value);
     // accumulated device time of the two step kernels since profiling was switched on (ms) and the step count
@@ -170,6 +174,8 @@ private:
     std::vector<void *> owned_;
     int32_t *d_worklist_ = nullptr;   // [W] scratch for reset lists
     float *h_pinned_actions_ = nullptr;
+    float *d_shaped_reward_ = nullptr;    // [W,S], allocated on first use
+    float *d_expert_actions_ = nullptr;   // [W,S,91,3 or 10], allocated on first use
     float *d_policy_obs_ = nullptr;       // [W,S,6 + (S-1)*6 + 200*13], allocated on first use
     float *d_act_stage_ = nullptr;        // [W*S*10] contiguous landing buffer of stepHost's actions
     cudaStream_t copy_stream_ = nullptr;  // stepHost: reward / done / info leave while k_obs still runs

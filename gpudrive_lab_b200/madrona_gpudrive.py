@@ -231,6 +231,36 @@ class SimManager:
         _capi.check(self._lib.gd_policy_obs(self._h, 1 if normalize else 0, C.byref(d)))
         return Tensor(d, self)
 
+    _REWARD_MODES = {"sparse_on_goal_achieved": 0, "weighted_combination": 1, "reward_conditioned": 2,
+                     "distance_to_logs": 3}
+
+    def shaped_reward_tensor(self, reward_type="weighted_combination", collision_weight=-0.5,
+                             goal_achieved_weight=1.0, off_road_weight=-0.5, log_distance_weight=0.01,
+                             agent_weights=None, world_time_steps=None) -> Tensor:
+        """GPUDriveTorchEnv.get_rewards (gpudrive/env/env_torch.py:469-604) in one device pass: f32 [W, S].
+        agent_weights: CUDA float32 tensor [W, S, 3] for "reward_conditioned"; world_time_steps: CUDA int32
+        tensor [W] for "distance_to_logs" (default: episode length - steps remaining)."""
+        def ptr(t, dtype):
+            if t is None:
+                return None
+            import torch
+            assert t.is_cuda and t.dtype == dtype and t.is_contiguous(), "need a contiguous CUDA tensor"
+            return t.data_ptr()
+        import torch
+        cfg = _capi.GdRewardShaping(self._REWARD_MODES[reward_type], collision_weight, goal_achieved_weight,
+                                    off_road_weight, log_distance_weight, ptr(agent_weights, torch.float32),
+                                    ptr(world_time_steps, torch.int32))
+        d = _capi.GdTensorDesc()
+        _capi.check(self._lib.gd_shaped_reward(self._h, C.byref(cfg), C.byref(d)))
+        return Tensor(d, self)
+
+    def expert_actions_tensor(self) -> Tensor:
+        """GPUDriveTorchEnv.get_expert_actions()[0] (env_torch.py:1445-1509): f32 [W, S, 91, 3] clamped inferred
+        actions, or [W, S, 91, 10] for the State dynamics model."""
+        d = _capi.GdTensorDesc()
+        _capi.check(self._lib.gd_expert_actions(self._h, C.byref(d)))
+        return Tensor(d, self)
+
     def launch_count(self) -> int:
         return int(self._lib.gd_launch_count(self._h))
 

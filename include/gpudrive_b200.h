@@ -131,6 +131,23 @@ int gd_step_host(GdHandle h, const float *actions, int32_t action_cols, float *r
  * (gpudrive/env/env_torch.py:756-891,1172-1216; normalisation constants gpudrive/env/constants.py).
  * out: f32 [W, S, 6 + (S-1)*6 + 200*13], valid until the next call. normalize = config.norm_obs. */
 int gd_policy_obs(GdHandle h, int32_t normalize, GdTensorDesc *out);
+/* Shaped reward of every agent slot, computed on the device from info / reward / expert_trajectory /
+ * absolute_self_observation in one pass: GPUDriveTorchEnv.get_rewards (gpudrive/env/env_torch.py:469-604).
+ * mode: 0 "sparse_on_goal_achieved" (the reward tensor), 1 "weighted_combination", 2 "reward_conditioned"
+ * (agent_weights: device f32 [W,S,3] = collision, goal_achieved, off_road), 3 "distance_to_logs"
+ * (world_time_steps: device i32 [W], or NULL for episode_len - steps_remaining). out: f32 [W,S], valid until the
+ * next call. */
+typedef struct GdRewardShaping {
+    int32_t mode;
+    float collision_weight, goal_achieved_weight, off_road_weight, log_distance_weight;
+    const float *agent_weights;
+    const int32_t *world_time_steps;
+} GdRewardShaping;
+int gd_shaped_reward(GdHandle h, const GdRewardShaping *cfg, GdTensorDesc *out);
+/* Expert actions of the logged trajectories: GPUDriveTorchEnv.get_expert_actions (env_torch.py:1445-1509).
+ * out: f32 [W,S,91,3] clamped inferred actions (Classic / InvertibleBicycle: +-6, +-0.3, -; DeltaLocal: +-6, +-6,
+ * +-pi) or [W,S,91,10] (x, y, 1, yaw, vx, vy, 0, 0, 0, 0) for the State model; valid until the next call. */
+int gd_expert_actions(GdHandle h, GdTensorDesc *out);
 /* Device scenario pool: load a scenario once, re-bind worlds to pooled scenarios + reset them. */
 int gd_pool_add(GdHandle h, const char *scene_path, int32_t *scene_id_out);
 int gd_bind_worlds(GdHandle h, const int32_t *worlds, const int32_t *scene_ids, int32_t n);

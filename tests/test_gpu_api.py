@@ -145,3 +145,53 @@ def test_binary_scenario_pool_equals_json(tmp_path):
     b.deleteAgents({0: [int(b.absolute_self_observation_tensor().to_torch()[0, 1, 13].item())]})
     a.deleteAgents({0: [int(a.absolute_self_observation_tensor().to_torch()[0, 1, 13].item())]})
     assert torch.equal(a.shape_tensor().to_torch(), b.shape_tensor().to_torch())
+
+
+def test_shaped_reward_and_expert_actions_match_reference_python(tmp_path):
+    """gd_shaped_reward / gd_expert_actions: on the golden inputs they reproduce what the
+    reference's own get_rewards / get_expert_actions returned (tests/golden/make_env_post_golden.py), and on
+    live tensors they equal the numpy restatement."""
+    import os
+    import torch
+    import env_post_ref as R
+    G = np.load(os.path.join(os.path.dirname(__file__), "golden", "env_post.npz"))
+    sa, sb = unpack(["synth_a", "synth_b"], tmp_path)
+
+    def bits(a):
+        return np.ascontiguousarray(a, dtype=np.float32).view(np.uint32)
+    kw = dict(collision_weight=-0.75, goal_achieved_weight=1.25, off_road_weight=-0.5, log_distance_weight=0.02)
+    modes = ("sparse_on_goal_achieved", "weighted_combination", "reward_conditioned", "distance_to_logs")
+    for model in range(4):
+        sim = _sim([sa, sb], param_dict(dynamicsModel=model, collisionBehaviour=0, maxNumControlledAgents=12))
+        A = G["info"].shape[1]
+        # golden inputs written over the exports (slots >= A keep the engine's values)
+        sim.info_tensor().to_torch()[:, :A] = torch.from_numpy(G["info"]).cuda()
+        sim.reward_tensor().to_torch()[:, :A] = torch.from_numpy(G["reward"]).cuda()
+        sim.expert_trajectory_tensor().to_torch()[:, :A] = torch.from_numpy(G["expert_trajectory"]).cuda()
+        sim.absolute_self_observation_tensor().to_torch()[:, :A] = torch.from_numpy(G["absolute_self_observation"]).cuda()
+        acts = sim.expert_actions_tensor().to_torch().cpu().numpy()
+        assert np.array_equal(bits(acts[:, :A]), bits(G["expert_actions_%d" % model])), model
+        if model:
+            continue
+        w = torch.zeros((2, 128, 3), dtype=torch.float32, device="cuda")
+        w[:, :A] = torch.from_numpy(G["agent_weights"]).cuda()
+        wts = torch.from_numpy(G["world_time_steps"]).cuda()
+        for mode in modes:
+            r = sim.shaped_reward_tensor(mode, agent_weights=w, world_time_steps=wts, **kw).to_torch().cpu().numpy()
+            want = G["reward_" + mode]
+            if mode == "distance_to_logs":
+                assert np.allclose(r[:, :A], want, rtol=1e-6, atol=1e-9), mode
+            else:
+                assert np.array_equal(bits(r[:, :A]), bits(want)), mode
+    # live tensors, default time step (episode length - steps remaining)
+    sim = _sim([sa, sb], param_dict(dynamicsModel=0, collisionBehaviour=0, maxNumControlledAgents=12))
+    for t in range(12):
+        sim.action_tensor().to_torch().copy_(torch.from_numpy(random_actions(t, 2, 128, 0, seed=23)).cuda())
+        sim.step()
+    snap = {n: getattr(sim, n + "_tensor")().to_torch().cpu().numpy()
+            for n in ("info", "reward", "expert_trajectory", "absolute_self_observation")}
+    for mode in ("weighted_combination", "distance_to_logs"):
+        r = sim.shaped_reward_tensor(mode, **kw).to_torch().cpu().numpy()
+        want = R.shaped_reward(snap["info"], snap["reward"], snap["expert_trajectory"], snap["absolute_self_observation"],
+                               mode, world_time_steps=np.array([12, 12]), **kw)
+        assert np.allclose(r, want, rtol=1e-6, atol=1e-9), mode
