@@ -103,18 +103,15 @@ __device__ __forceinline__ float rcp_fast(float x) {
 __device__ __forceinline__ float ray_box(float px, float py, float cphi, float sphi, float d0, float d1,
                                          float dx, float dy)
 {
+    // Branch-free slabs. A direction component of exactly 0 gives an infinite reciprocal: both slab
+    // parameters become -inf / +inf (origin between the planes: no constraint) or the same infinity (origin
+    // outside: tnear > tfar, a miss); fminf / fmaxf drop the NaN of 0 * inf (origin exactly on a plane).
     const float lx = fmaf(cphi, dx, sphi * dy), ly = fmaf(cphi, dy, -(sphi * dx));   // direction in box frame
-    float tnear = -1.f, tfar = kLidarDistance;
-    if (lx != 0.f) {
-        const float inv = rcp_fast(lx);
-        const float t1 = (-d0 - px) * inv, t2 = (d0 - px) * inv;
-        tnear = fminf(t1, t2); tfar = fminf(tfar, fmaxf(t1, t2));
-    } else if (fabsf(px) > d0) return -1.f;
-    if (ly != 0.f) {
-        const float inv = rcp_fast(ly);
-        const float t1 = (-d1 - py) * inv, t2 = (d1 - py) * inv;
-        tnear = fmaxf(tnear, fminf(t1, t2)); tfar = fminf(tfar, fmaxf(t1, t2));
-    } else if (fabsf(py) > d1) return -1.f;
+    const float ivx = rcp_fast(lx), ivy = rcp_fast(ly);
+    const float x1 = (-d0 - px) * ivx, x2 = (d0 - px) * ivx;
+    const float y1 = (-d1 - py) * ivy, y2 = (d1 - py) * ivy;
+    const float tnear = fmaxf(fminf(x1, x2), fminf(y1, y2));
+    const float tfar = fminf(kLidarDistance, fminf(fmaxf(x1, x2), fmaxf(y1, y2)));
     return (tnear >= 0.f && tnear <= tfar) ? tnear : -1.f;
 }
 
@@ -168,37 +165,39 @@ __device__ __forceinline__ bool ray_range(float a, float w, int &lo, int &hi) {
     const float inv_delta = (float)NRAY / (2.f * kLidarAngle);
     const float half = 0.5f * (float)(NRAY - 1);
     const float flo = fmaf(a - w, inv_delta, half), fhi = fmaf(a + w, inv_delta, half);
-    if (fhi < 0.f || flo > (float)(NRAY - 1)) return false;
-    lo = max(0, (int)ceilf(flo));
-    hi = min(NRAY - 1, (int)floorf(fhi));
-    return lo <= hi;
+    lo = max(0, __float2int_ru(flo));
+    hi = min(NRAY - 1, __float2int_rd(fhi));
+    return !(fhi < 0.f) && !(flo > (float)(NRAY - 1)) && lo <= hi;
 }
 
 // Which rays can touch this box? Conservative: never drops a ray the exact clip would accept.
 // Returns false if none, else the ray index range [lo, hi]. (relx, rely): box centre relative to the ray
-// origin; (cphi, sphi): box axis.
+// origin; (cphi, sphi): box axis. Written without early exits: in a warp some lane needs every step anyway,
+// and straight-line code with selects is cheaper than the divergence bookkeeping of the branches.
 __device__ __forceinline__ bool lidar_consider(const LidarCtx &c, float relx, float rely, float cphi, float sphi,
                                                float d0, float d1, int &lo, int &hi)
 {
     const float rbound = d0 + d1;                         // >= half diagonal
     const float D2 = fmaf(relx, relx, rely * rely);
     const float range = kLidarDistance + rbound;
-    if (!(D2 <= range * range)) return false;
+    const bool in_range = D2 <= range * range;
     const float fx = fmaf(c.fc, relx, c.fs * rely), fy = fmaf(c.fc, rely, -(c.fs * relx));   // centre in the fan frame
-    lo = 0; hi = NRAY - 1;
     // box half axes e0 = d0 (cphi, sphi), e1 = d1 (-sphi, cphi)
     const float along = fmaf(relx, cphi, rely * sphi), across = fmaf(rely, cphi, -(relx * sphi));
     const float maxcross = fmaf(d0, fabsf(across), d1 * fabsf(along));
     const float mindot = D2 - fmaf(d0, fabsf(along), d1 * fabsf(across));
     const bool close_box = !(mindot > 1e-6f * D2) || D2 <= (rbound + 0.01f) * (rbound + 0.01f);
-    if (close_box) return true;
     const float cH = 0.5146014f, sH = 0.8574295f;     // cos / sin of 24.5 * delta + 4e-3 (fan half angle)
-    if (fx < -rbound) return false;                   // behind the fan
-    if (fmaf(cH, fy, -(sH * fx)) > rbound) return false;     // beyond the last ray
-    if (fmaf(cH, fy, sH * fx) < -rbound) return false;       // before the first ray
+    const bool outside = fx < -rbound                                  // behind the fan
+                         || fmaf(cH, fy, -(sH * fx)) > rbound           // beyond the last ray
+                         || fmaf(cH, fy, sH * fx) < -rbound;            // before the first ray
     const float w = maxcross * rcp_fast(mindot);      // tan of the half width; atan(w) <= w
-    if (w < 1.0f) return ray_range(fast_atan2(fy, fx), w * 1.0001f + 2e-3f, lo, hi);
-    return true;
+    int lo2, hi2;
+    const bool some = ray_range(fast_atan2(fy, fx), w * 1.0001f + 2e-3f, lo2, hi2);
+    const bool narrow = !close_box && w < 1.0f;
+    lo = narrow ? lo2 : 0;
+    hi = narrow ? hi2 : NRAY - 1;
+    return in_range && (close_box || (!outside && (!narrow || some)));
 }
 
 // z-slab membership of the three lidar planes for a hull with object-space z in [zmin_obj, zmax_obj]
@@ -262,16 +261,18 @@ __device__ __forceinline__ void lidar_expand(ObsWarpSmem &wp, int lane, int lo, 
             const float t = ray_box(spx, spy, sc_, ss_, sd0, sd1, d.x, d.y);
             if (t >= 0.f) {
                 tb = __float_as_uint(t);
-                for (int q = spm; q; q &= q - 1) atomicMin(&wp.u.l.bt[(__ffs(q) - 1) * NRAY + ray], tb);
+                if (spm & 1) atomicMin(&wp.u.l.bt[ray], tb);
+                if (spm & 2) atomicMin(&wp.u.l.bt[NRAY + ray], tb);
+                if (spm & 4) atomicMin(&wp.u.l.bt[2 * NRAY + ray], tb);
             }
         }
         GD_CNT(9, 1);
         __syncwarp();
         if (tb != 0xffffffffu) {
-            for (; spm; spm &= spm - 1) {
-                const int k = (__ffs(spm) - 1) * NRAY + ray;
-                if (wp.u.l.bt[k] == tb) wp.u.l.bid[k] = (uint16_t)(smeta >> 15);
-            }
+            const uint16_t bid = (uint16_t)(smeta >> 15);
+            if ((spm & 1) && wp.u.l.bt[ray] == tb) wp.u.l.bid[ray] = bid;
+            if ((spm & 2) && wp.u.l.bt[NRAY + ray] == tb) wp.u.l.bid[NRAY + ray] = bid;
+            if ((spm & 4) && wp.u.l.bt[2 * NRAY + ray] == tb) wp.u.l.bid[2 * NRAY + ray] = bid;
         }
     }
     __syncwarp();
