@@ -126,26 +126,26 @@ __device__ __forceinline__ float ray_box_exact(float ox, float oy, float bx, flo
     lox = __fdiv_rn(lox, d0); loy = __fdiv_rn(loy, d1);
     inv_rotate_xy(qw, qz, dirx, diry, ldx, ldy);
     ldx = __fdiv_rn(ldx, d0); ldy = __fdiv_rn(ldy, d1);
+    // The four vertical faces in the reference's order (+x, -x, +y, -y), without its early exits: a miss is
+    // a sticky flag, so the planes after it cannot change the outcome.
     float tfirst = 0.f, tlast = kLidarDistance;
-    bool entered = false;
+    bool entered = false, miss = false;
 #pragma unroll
     for (int k = 0; k < 4; k++) {
         const float sgn = (k & 1) ? -1.f : 1.f;
         const float denom = sgn * ((k < 2) ? ldx : ldy);
         const float neg_dist = __fsub_rn(1.f, sgn * ((k < 2) ? lox : loy));
-        if (denom == 0.0f) {
-            if (neg_dist < 0.0f) return -1.f;
-        } else {
-            const float t = __fdiv_rn(neg_dist, denom);
-            if (denom < 0.0f) {
-                if (t >= tfirst) { tfirst = t; entered = true; }
-            } else {
-                if (t <= tlast) tlast = t;
-            }
-            if (tfirst > tlast) return -1.f;
-        }
+        const bool par = denom == 0.0f;
+        const float t = __fdiv_rn(neg_dist, denom);
+        miss = miss || (par && neg_dist < 0.0f);
+        const bool enter = !par && denom < 0.0f && t >= tfirst;
+        const bool leave = !par && denom > 0.0f && t <= tlast;
+        tfirst = enter ? t : tfirst;
+        tlast = leave ? t : tlast;
+        entered = entered || enter;
+        miss = miss || (!par && tfirst > tlast);
     }
-    return entered ? tfirst : -1.f;
+    return (entered && !miss) ? tfirst : -1.f;
 }
 
 // atan2 with |error| < 2e-4 rad (odd minimax polynomial on [0, 1] + octant folding)
@@ -297,7 +297,6 @@ __device__ __forceinline__ void open_rays(const uint32_t *best, float dist, int 
 __device__ __forceinline__ void flush_rows(float *stage, float *dst, const float (&row)[9], bool has_row,
                                            int rank, int m, int lane)
 {
-    __syncwarp();
     if (has_row) {
 #pragma unroll
         for (int k = 0; k < 9; k++) stage[rank * 9 + k] = row[k];

@@ -79,24 +79,22 @@ k_obs(const SceneDev *__restrict__ scenes, StateDev st, Exports ex, Params prm, 
             const int jp = base + lane;
             const bool has = jp < P;
             float row[9];
-            if (has && jp < A - 1) {
-                const int j = jp < a ? jp : jp + 1;       // OtherAgents order, level_gen.cpp:450-464
+            row[0] = row[1] = row[2] = row[3] = row[4] = row[5] = row[6] = row[7] = 0.f;
+            row[8] = -2.f;                                            // zero_nonexist()
+            if (base < A - 1) {       // (warp-uniform) straight-line inside: some lane takes each path anyway
+                const bool exists = has && jp < A - 1;
+                const int j = exists ? (jp < a ? jp : jp + 1) : 0;   // OtherAgents order, level_gen.cpp:450-464
                 const float4 o0 = sm.a0[j], o1 = sm.a1[j];
-                float rx, ry;
+                const float4 o3 = sc.ag_a[j];
+                float rx, ry, rw, rz;
                 inv_rotate_xy(qw, qz, __fsub_rn(o0.x, px), __fsub_rn(o0.y, py), rx, ry);
-                if (__fsqrt_rn(len2_xy(rx, ry)) > radius) {
-                    row[0] = row[1] = row[2] = row[3] = row[4] = row[5] = row[6] = row[7] = 0.f;
-                    row[8] = -1.f;                          // PartnerObservation::zero()
-                } else {
-                    const float4 o3 = sc.ag_a[j];
-                    float rw, rz;
-                    inv_mul_quat(qw, qz, o0.z, o0.w, rw, rz);
-                    row[0] = o1.y; row[1] = rx; row[2] = ry; row[3] = quat_to_yaw(rw, rz);
-                    row[4] = o3.x; row[5] = o3.y; row[6] = o3.z; row[7] = o1.z; row[8] = o1.w;
-                }
-            } else {
-                row[0] = row[1] = row[2] = row[3] = row[4] = row[5] = row[6] = row[7] = 0.f;
-                row[8] = -2.f;                              // zero_nonexist()
+                inv_mul_quat(qw, qz, o0.z, o0.w, rw, rz);
+                const bool seen = exists && !(__fsqrt_rn(len2_xy(rx, ry)) > radius);
+                row[0] = seen ? o1.y : 0.f; row[1] = seen ? rx : 0.f; row[2] = seen ? ry : 0.f;
+                row[3] = seen ? quat_to_yaw(rw, rz) : 0.f;
+                row[4] = seen ? o3.x : 0.f; row[5] = seen ? o3.y : 0.f; row[6] = seen ? o3.z : 0.f;
+                row[7] = seen ? o1.z : 0.f;
+                row[8] = seen ? o1.w : (exists ? -1.f : -2.f);       // PartnerObservation::zero()
             }
             const int m = min(32, P - base);
             flush_rows(wp.u.stage, dstbase + (size_t)base * 9, row, has, lane, m, lane);
@@ -242,38 +240,29 @@ k_obs(const SceneDev *__restrict__ scenes, StateDev st, Exports ex, Params prm, 
                     if (do_l || first_k_only) c = __ldg(&sc.s_c[e]);
                     if (do_n) {
                         const float dx = __fsub_rn(ra.x, px), dy = __fsub_rn(ra.y, py);
-                        bool in = false; float key = 0.f;
-                        if (fabsf(dx) <= rpad && fabsf(dy) <= rpad) {
-                            float ox, oy;
-                            inv_rotate_xy(qw, qz, dx, dy, ox, oy);
-                            key = len2_xy(ox, oy);
-                            in = key <= key_thr;
-                        }
+                        float ox, oy;
+                        inv_rotate_xy(qw, qz, dx, dy, ox, oy);
+                        const float key = len2_xy(ox, oy);
+                        const bool in = key <= key_thr;         // (a far-away dummy slot gives inf: never in)
                         const unsigned inm = __ballot_sync(FULL, in);
-                        if (in) {
-                            const int pos = cnt + __popc(inm & lt_mask);
-                            if (pos < OBS_CAND) {
-                                wp.ckey[pos] = first_k_only ? (c >> 16) : __float_as_uint(key);
-                                wp.cpos[pos] = (uint16_t)e;
-                            }
+                        const int pos = cnt + __popc(inm & lt_mask);
+                        if (in && pos < OBS_CAND) {
+                            wp.ckey[pos] = first_k_only ? (c >> 16) : __float_as_uint(key);
+                            wp.cpos[pos] = (uint16_t)e;
                         }
                         cnt += __popc(inm);
                     }
                     if (do_l) {
                         const int pm = (zmask_classes >> (3 * (int)(c & 0xffu))) & 7;
-                        int lo = 0, n = 0;
-                        float2 rb = make_float2(1.f, 1.f);
+                        const float2 rb = __ldg(&sc.s_b[e]);
                         const float relx = ra.x - px, rely = ra.y - py;
                         const float cphi = 1.f - 2.f * ra.w * ra.w, sphi = 2.f * ra.z * ra.w;
-                        if (pm) {
-                            rb = __ldg(&sc.s_b[e]);
-                            int hi;
-                            if (lidar_consider(lc, relx, rely, cphi, sphi, rb.x, rb.y, lo, hi)) {
-                                // trim the range to its first / last open ray (closed rays inside are clipped too)
-                                const unsigned long long m = ray_bits(lo, hi) & open_for(open, pm);
-                                if (m) { lo = __ffsll((long long)m) - 1; n = 64 - __clzll((long long)m) - lo; }
-                            }
-                        }
+                        int lo, hi;
+                        const bool some = lidar_consider(lc, relx, rely, cphi, sphi, rb.x, rb.y, lo, hi);
+                        // trim the range to its first / last open ray (closed rays inside are clipped too)
+                        const unsigned long long m = (pm && some) ? (ray_bits(lo, hi) & open_for(open, pm)) : 0ull;
+                        lo = m ? __ffsll((long long)m) - 1 : 0;
+                        const int n = m ? 64 - __clzll((long long)m) - lo : 0;
                         lidar_expand(wp, lane, lo, n, pm, (unsigned)e, relx, rely, cphi, sphi, rb.x, rb.y);
                     }
                 }
