@@ -45,3 +45,18 @@ def build_engine(force: bool = False, verbose: bool = False) -> str:
     if verbose:
         print(r.stderr)
     return OUT
+
+
+HEADLESS = os.path.join(HERE, "gd_headless")
+
+
+def build_headless() -> str:
+    """tools/gd_headless.cpp: the C++ counterpart of the reference's `headless` executable, linked against
+    the C ABI only (plus cudart for two copies)."""
+    src = os.path.join(HERE, "..", "tools", "gd_headless.cpp")
+    cmd = [_nvcc(), "-O2", "-std=c++17", "-o", HEADLESS, src, "-L" + HERE, "-lgpudrive_b200",
+           "-Xlinker", "-rpath," + HERE]
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    if r.returncode != 0:
+        raise RuntimeError("gd_headless build failed:\n" + r.stdout + r.stderr)
+    return HEADLESS

@@ -38,7 +38,20 @@ constexpr int OBS_BLOCK = OBS_WARPS * 32;
 constexpr int OBS_CAND = 512;             // in-radius candidates kept per agent before the slow path
 constexpr int OBS_GCAP = 128;             // group descriptors per pass (4 per lane; larger maps take several passes)
 constexpr int NRAY = kNumLidarSamples;    // 50
-constexpr int NBAND = 7;                  // distance bands: [0,4) [4,8) [8,16) [16,32) [32,64) [64,128) [128,inf)
+#ifndef GD_OBS_BANDS
+#define GD_OBS_BANDS 7
+#endif
+constexpr int NBAND = GD_OBS_BANDS;       // distance bands: 7: [0,4) [4,8) [8,16) [16,32) [32,64) [64,128) [128,inf)
+                                          //                 4: [0,4) [4,16) [16,64) [64,inf)
+// band of a group whose nearest point is dmin away (e = floor(log2(dmin))), and the lower edge of a band
+__device__ __forceinline__ int obs_band_of(float dmin, int e) {
+    if (NBAND == 7) return dmin < 4.f ? 0 : min(NBAND - 1, e - 1);
+    return dmin < 4.f ? 0 : min(NBAND - 1, e >> 1);
+}
+__device__ __forceinline__ float obs_band_lo(int band) {
+    if (NBAND == 7) return band == 0 ? 0.f : (float)(2 << band);
+    return band == 0 ? 0.f : (float)(1 << (2 * band));
+}
 constexpr unsigned long long RAY_ALL = (1ull << NRAY) - 1ull;
 
 struct ObsWarpSmem {

@@ -170,32 +170,32 @@ k_obs(const SceneDev *__restrict__ scenes, StateDev st, Exports ex, Params prm, 
         __syncwarp();
         for (int base = 0; base < gN; base += 32) {
             const int gl = base + lane;
-            uint32_t desc = 0; bool keep = false;
-            if (gl < gN) {
-                const float4 gc = __ldg(&sc.grp[g0 + gl]);
-                const float relx = gc.x - px, rely = gc.y - py;
-                const float d = sqrtf(relx * relx + rely * rely);
-                const float dmin = fmaxf(d - gc.z, 0.f);
-                const bool nearg = want_cands && dmin <= rpad;
-                int pmg = 0, lo = 0, hi = NRAY - 1;
-                if (lidar_on && dmin <= kLidarDistance) {
-                    for (unsigned cm = __float_as_uint(gc.w) & 0xffu; cm; cm &= cm - 1)      // usually one class
-                        pmg |= (zmask_classes >> (3 * (__ffs(cm) - 1))) & 7;
-                    if (pmg && d > gc.z * 1.0001f + 0.01f) {
-                        const float s = gc.z / d;                                   // sin of the half width
-                        const float w = s * rsqrtf(fmaxf(1.f - s * s, 1e-6f));      // tan >= the angle itself
-                        if (w < 3.f) {
-                            const float fx = lc.fc * relx + lc.fs * rely, fy = lc.fc * rely - lc.fs * relx;
-                            if (!ray_range(fast_atan2(fy, fx), w + 2e-3f, lo, hi)) pmg = 0;
-                        }
-                    }
-                }
-                keep = nearg || pmg != 0;
-                const int e = (int)(__float_as_uint(dmin) >> 23) - 127;           // floor(log2(dmin))
-                const int band = dmin < 4.f ? 0 : min(NBAND - 1, e - 1);
-                desc = (uint32_t)gl | ((uint32_t)band << 12) | ((uint32_t)lo << 15) | ((uint32_t)hi << 21) |
-                       (nearg ? (1u << 27) : 0u) | ((uint32_t)pmg << 28);
-            }
+            const bool valid = gl < gN;
+            // straight-line: selects instead of branches (a warp has lanes on every path)
+            const float4 gc = __ldg(&sc.grp[g0 + (valid ? gl : 0)]);
+            const float relx = gc.x - px, rely = gc.y - py;
+            const float d2 = fmaf(relx, relx, rely * rely);
+            const float d = sqrtf(d2);
+            const float dmin = fmaxf(d - gc.z, 0.f);
+            const bool nearg = valid && want_cands && dmin <= rpad;
+            const unsigned cm = __float_as_uint(gc.w) & 0xffu;       // one z-class per group (classes are padded to 32)
+            int pmg = (lidar_on && valid && cm && dmin <= kLidarDistance) ? (zmask_classes >> (3 * (__ffs(cm) - 1))) & 7 : 0;
+            const float fx = fmaf(lc.fc, relx, lc.fs * rely), fy = fmaf(lc.fc, rely, -(lc.fs * relx));
+            const bool apart = d > gc.z * 1.0001f + 0.01f;          // the origin is outside the circle
+            const float cH = 0.5146014f, sH = 0.8574295f;            // fan half angle, as in lidar_consider
+            const bool outside = fx < -gc.z || fmaf(cH, fy, -(sH * fx)) > gc.z || fmaf(cH, fy, sH * fx) < -gc.z;
+            const float sn = gc.z * rcp_fast(fmaxf(d, 1e-20f));                 // sin of the half width
+            const float w = sn * rsqrtf(fmaxf(1.f - sn * sn, 1e-6f));           // tan >= the angle itself
+            int lo2, hi2;
+            const bool some = ray_range(fast_atan2(fy, fx), w * 1.0001f + 2e-3f, lo2, hi2);
+            const bool narrow = apart && w < 3.f;
+            if (apart && (outside || (narrow && !some))) pmg = 0;
+            const int lo = narrow ? lo2 : 0, hi = narrow ? hi2 : NRAY - 1;
+            const bool keep = nearg || pmg != 0;
+            const int e = (int)(__float_as_uint(dmin) >> 23) - 127;           // floor(log2(dmin))
+            const int band = obs_band_of(dmin, e);
+            const uint32_t desc = !keep ? 0u : (uint32_t)gl | ((uint32_t)band << 12) | ((uint32_t)lo << 15) | ((uint32_t)hi << 21) |
+                                  (nearg ? (1u << 27) : 0u) | ((uint32_t)pmg << 28);
             const unsigned km = __ballot_sync(FULL, keep);
             if (keep) wp.v.g.glist[nlist + __popc(km & lt_mask)] = desc;
             nlist += __popc(km);
@@ -207,7 +207,7 @@ k_obs(const SceneDev *__restrict__ scenes, StateDev st, Exports ex, Params prm, 
         GD_CNT(0, 1); GD_CNT(1, nlist);
         // ---- bands of increasing distance
         for (int band = 0; band < NBAND; band++) {
-            const float band_lo = band == 0 ? 0.f : (float)(2 << band);
+            const float band_lo = obs_band_lo(band);
             // rays with no hit nearer than the band: only these can still be improved from here on
             if (lidar_on) open_rays(wp.u.l.bt, band_lo * 0.9999f - 1e-3f, lane, open);
             const bool any_open = lidar_on && (open[0] | open[1] | open[2]) != 0ull;
@@ -235,9 +235,11 @@ k_obs(const SceneDev *__restrict__ scenes, StateDev st, Exports ex, Params prm, 
                     const bool do_n = (nrm >> src) & 1u;
                     const int e = gid * 32 + lane;
                     GD_CNT(2, 1); GD_CNT(3, do_l ? 1 : 0); GD_CNT(4, do_n ? 1 : 0);
+                    // all three columns up front, so their latencies overlap (the kNN-only passes pay two
+                    // loads they do not need; they hit L1 / L2)
                     const float4 ra = __ldg(&sc.s_a[e]);
-                    uint32_t c = 0;
-                    if (do_l || first_k_only) c = __ldg(&sc.s_c[e]);
+                    const uint32_t c = __ldg(&sc.s_c[e]);
+                    const float2 rb = __ldg(&sc.s_b[e]);
                     if (do_n) {
                         const float dx = __fsub_rn(ra.x, px), dy = __fsub_rn(ra.y, py);
                         float ox, oy;
@@ -254,7 +256,6 @@ k_obs(const SceneDev *__restrict__ scenes, StateDev st, Exports ex, Params prm, 
                     }
                     if (do_l) {
                         const int pm = (zmask_classes >> (3 * (int)(c & 0xffu))) & 7;
-                        const float2 rb = __ldg(&sc.s_b[e]);
                         const float relx = ra.x - px, rely = ra.y - py;
                         const float cphi = 1.f - 2.f * ra.w * ra.w, sphi = 2.f * ra.z * ra.w;
                         int lo, hi;
@@ -481,7 +482,7 @@ k_obs(const SceneDev *__restrict__ scenes, StateDev st, Exports ex, Params prm, 
         int m = __popc(am);
         if (emitted + m > K) { m = K - emitted; if (rank >= m) acc = false; }
         float row[9];
-        if (acc) {
+        {   // straight-line (most lanes of a chunk emit a row; e is a valid slot on the others)
             const float4 ra = __ldg(&sc.s_a[e]); const float2 rb = __ldg(&sc.s_b[e]);
             const float4 rd = __ldg(&sc.s_d[e]);
             float ox, oy, rw, rz;
@@ -489,7 +490,7 @@ k_obs(const SceneDev *__restrict__ scenes, StateDev st, Exports ex, Params prm, 
             inv_mul_quat(qw, qz, ra.z, ra.w, rw, rz);
             row[0] = ox; row[1] = oy; row[2] = rb.x; row[3] = rb.y; row[4] = rd.x;
             row[5] = quat_to_yaw(rw, rz); row[6] = (float)((rc >> 8) & 0xffu); row[7] = rd.z; row[8] = rd.w;
-            if (write_knn_idx) kidx[emitted + rank] = (int32_t)(rc >> 16);
+            if (acc && write_knn_idx) kidx[emitted + rank] = (int32_t)(rc >> 16);
         }
         flush_rows(wp.u.stage, rows + (size_t)emitted * 9, row, acc, rank, m, lane);
         emitted += m;
