@@ -80,3 +80,14 @@ def test_install_registers_module():
     import madrona_gpudrive
     assert madrona_gpudrive.SimManager is gpudrive_lab_b200.madrona_gpudrive.SimManager
     sys.modules.pop("madrona_gpudrive", None)
+
+
+def test_headless_cli_builds_and_refuses_cpu():
+    """tools/gd_headless.cpp (counterpart of src/headless.cpp) links against the C ABI alone."""
+    import subprocess
+    from gpudrive_lab_b200 import build
+    exe = build.build_headless()
+    r = subprocess.run([exe, "CPU", "3"], capture_output=True, text=True)
+    assert r.returncode != 0 and "no CPU backend" in r.stderr
+    r = subprocess.run([exe], capture_output=True, text=True)
+    assert r.returncode != 0 and "NUM_STEPS" in r.stderr

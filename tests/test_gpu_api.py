@@ -195,3 +195,19 @@ def test_shaped_reward_and_expert_actions_match_reference_python(tmp_path):
         want = R.shaped_reward(snap["info"], snap["reward"], snap["expert_trajectory"], snap["absolute_self_observation"],
                                mode, world_time_steps=np.array([12, 12]), **kw)
         assert np.allclose(r, want, rtol=1e-6, atol=1e-9), mode
+
+
+def test_headless_cli_runs(tmp_path):
+    """The C++ driver steps real worlds through the C ABI and reports the reference's two FPS lines."""
+    import re
+    import subprocess
+    from gpudrive_lab_b200 import build
+    exe = build.HEADLESS if __import__("os").path.exists(build.HEADLESS) else build.build_headless()
+    sa, sb = unpack(["synth_a", "synth_b"], tmp_path)
+    r = subprocess.run([exe, "CUDA", "20", "--rand-actions", "--worlds", "6", "--scenes", sa, sb],
+                       capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stderr
+    fps = float(re.search(r"^FPS ([0-9.]+)", r.stdout, re.M).group(1))
+    afps = float(re.search(r"^Agent-Normalized FPS ([0-9.]+)", r.stdout, re.M).group(1))
+    m = re.search(r"steps (\d+) agent_steps (\d+)", r.stdout)
+    assert fps > 0 and afps > fps and int(m.group(1)) == 20 and int(m.group(2)) > 0
