@@ -208,7 +208,7 @@ int Engine::uploadScene(const SceneData &s, const std::string &key) {
     auto section = [&](size_t bytes) { size_t o = off; off += (bytes + 15) & ~size_t(15); return o; };
     const size_t o_sa = section(sizeof(float4) * RS), o_sb = section(sizeof(float2) * RS),
                  o_sc = section(sizeof(uint32_t) * RS), o_sd = section(sizeof(float4) * RS),
-                 o_gr = section(sizeof(float4) * std::max(G, 1));
+                 o_gr = section(sizeof(float4) * 2 * std::max(G, 1));
     const size_t o_ra = section(sizeof(float4) * Rpad), o_rb = section(sizeof(float2) * Rpad),
                  o_rc = section(sizeof(uint32_t) * Rpad), o_rd = section(sizeof(float4) * Rpad),
                  o_cc = section(sizeof(float4) * Cpad), o_co = section(sizeof(float4) * 4 * Cpad),
@@ -246,26 +246,53 @@ int Engine::uploadScene(const SceneData &s, const std::string &key) {
             }
         }
         for (int g = 0; g < G; g++) {
-            float lox = 3e38f, loy = 3e38f, hix = -3e38f, hiy = -3e38f;
+            // bounds of the group's boxes: an oriented rectangle along the principal axis of their corners
+            // (polyline runs are long and thin) for distances, and the circle around its centre for angles
+            std::vector<float> px, py;
             uint32_t cmask = 0;
             for (int k = 0; k < 32; k++) {
                 const int r = sorted[g * 32 + k];
                 if (r < 0) continue;
-                lox = std::min(lox, s.rx[r]); hix = std::max(hix, s.rx[r]);
-                loy = std::min(loy, s.ry[r]); hiy = std::max(hiy, s.ry[r]);
                 cmask |= 1u << zcls[r];
+                const float c = 1.f - 2.f * s.rqz[r] * s.rqz[r], sn = 2.f * s.rqw[r] * s.rqz[r];
+                for (int q = 0; q < 4; q++) {
+                    const float ex = (q & 1) ? s.rd0[r] : -s.rd0[r], ey = (q & 2) ? s.rd1[r] : -s.rd1[r];
+                    px.push_back(s.rx[r] + ex * c - ey * sn);
+                    py.push_back(s.ry[r] + ex * sn + ey * c);
+                }
             }
-            const float cx = 0.5f * (lox + hix), cy = 0.5f * (loy + hiy);
-            float rad = 0.f;
-            for (int k = 0; k < 32; k++) {
-                const int r = sorted[g * 32 + k];
-                if (r < 0) continue;
-                const float dx = s.rx[r] - cx, dy = s.ry[r] - cy;
-                rad = std::max(rad, sqrtf(dx * dx + dy * dy) + s.rd0[r] + s.rd1[r]);
+            float4 circ = make_float4(1e30f, 1e30f, 0.f, 0.f), rect = make_float4(1.f, 0.f, 0.f, 0.f);
+            if (!px.empty()) {
+                double mx = 0, my = 0;
+                for (size_t i = 0; i < px.size(); i++) { mx += px[i]; my += py[i]; }
+                mx /= px.size(); my /= px.size();
+                double sxx = 0, sxy = 0, syy = 0;
+                for (size_t i = 0; i < px.size(); i++) {
+                    const double dx = px[i] - mx, dy = py[i] - my;
+                    sxx += dx * dx; sxy += dx * dy; syy += dy * dy;
+                }
+                const double th = 0.5 * atan2(2 * sxy, sxx - syy);
+                const float ux = (float)cos(th), uy = (float)sin(th);
+                float ulo = 3e38f, uhi = -3e38f, vlo = 3e38f, vhi = -3e38f;
+                for (size_t i = 0; i < px.size(); i++) {
+                    const float u = px[i] * ux + py[i] * uy, v = py[i] * ux - px[i] * uy;
+                    ulo = std::min(ulo, u); uhi = std::max(uhi, u); vlo = std::min(vlo, v); vhi = std::max(vhi, v);
+                }
+                const float cu = 0.5f * (ulo + uhi), cv = 0.5f * (vlo + vhi);
+                const float cx = cu * ux - cv * uy, cy = cu * uy + cv * ux;
+                // margins: the rectangle is evaluated in float on coordinates of a few thousand metres
+                const float ha = 0.5f * (uhi - ulo) * 1.0001f + 5e-3f, hb = 0.5f * (vhi - vlo) * 1.0001f + 5e-3f;
+                float rad = 0.f;
+                for (size_t i = 0; i < px.size(); i++) {
+                    const float dx = px[i] - cx, dy = py[i] - cy;
+                    rad = std::max(rad, sqrtf(dx * dx + dy * dy));
+                }
+                circ = make_float4(cx, cy, rad * 1.0001f + 5e-3f, 0.f);
+                rect = make_float4(ux, uy, ha, hb);
             }
-            float4 v = make_float4(cx, cy, rad * 1.0001f + 1e-3f, 0.f);
-            memcpy(&v.w, &cmask, 4);
-            gr[g] = v;
+            memcpy(&circ.w, &cmask, 4);
+            gr[2 * g] = circ;
+            gr[2 * g + 1] = rect;
         }
     }
     for (int i = 0; i < C; i++) {

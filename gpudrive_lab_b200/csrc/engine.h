@@ -29,7 +29,8 @@ struct SceneDev {
     const float2 *s_b;        // [G*32] d0, d1
     const uint32_t *s_c;      // [G*32] zclass | type << 8 | original road index << 16   (dummy: zclass 8)
     const float4 *s_d;        // [G*32] d2, yaw(heading), id, mapType
-    const float4 *grp;        // [G] bounding circle cx, cy, r (covers every member box) | z-class bit mask
+    const float4 *grp;        // [G][2] bounds of the group's boxes: circle cx, cy, r | z-class bit mask, then the
+                              //        rectangle around the same centre: axis ux, uy, half extents a, b
     const float4 *coll_cull;  // [Cpad] cx, cy, bounding radius, type
     const float4 *coll_obb;   // [Cpad*4] corners(8) | axes(4) | origin(2) z dz
     const float *traj;        // [A][1456]

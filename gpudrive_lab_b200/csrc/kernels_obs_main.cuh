@@ -172,11 +172,16 @@ k_obs(const SceneDev *__restrict__ scenes, StateDev st, Exports ex, Params prm, 
             const int gl = base + lane;
             const bool valid = gl < gN;
             // straight-line: selects instead of branches (a warp has lanes on every path)
-            const float4 gc = __ldg(&sc.grp[g0 + (valid ? gl : 0)]);
+            const float4 gc = __ldg(&sc.grp[2 * (g0 + (valid ? gl : 0))]);
+            const float4 gb = __ldg(&sc.grp[2 * (g0 + (valid ? gl : 0)) + 1]);
             const float relx = gc.x - px, rely = gc.y - py;
             const float d2 = fmaf(relx, relx, rely * rely);
             const float d = sqrtf(d2);
-            const float dmin = fmaxf(d - gc.z, 0.f);
+            // nearest point of the group: distance to its oriented rectangle (tighter than the circle for the
+            // long thin runs of a polyline); the circle serves the angular tests below
+            const float gex = fmaxf(fabsf(fmaf(relx, gb.x, rely * gb.y)) - gb.z, 0.f);
+            const float gey = fmaxf(fabsf(fmaf(rely, gb.x, -(relx * gb.y))) - gb.w, 0.f);
+            const float dmin = fmaxf(sqrtf(fmaf(gex, gex, gey * gey)), fmaxf(d - gc.z, 0.f));
             const bool nearg = valid && want_cands && dmin <= rpad;
             const unsigned cm = __float_as_uint(gc.w) & 0xffu;       // one z-class per group (classes are padded to 32)
             int pmg = (lidar_on && valid && cm && dmin <= kLidarDistance) ? (zmask_classes >> (3 * (__ffs(cm) - 1))) & 7 : 0;
