@@ -356,6 +356,7 @@ int Engine::uploadScene(const SceneData &s, const std::string &key) {
     scenes_.push_back(h);
     scene_index_[key] = (int)scenes_.size() - 1;
     max_roads_ = std::max(max_roads_, R);
+    max_scene_agents_ = std::max(max_scene_agents_, A);
     scene_table_dirty_ = true;
     return (int)scenes_.size() - 1;
 }
@@ -426,7 +427,8 @@ void Engine::launchRest(bool decrement) {
                                                                     decrement ? 1 : 0, decrement ? 1 : 0);
     if (prof) GD_CUDA(cudaEventRecord(ev[1], stream_));
     if (mark_agents_done_) GD_CUDA(cudaEventRecord(ev_agents_, stream_));   // reward / done / info are final here
-    const int groups = (S_ + OBS_WARPS - 1) / OBS_WARPS;
+    // CTAs only for slots some pooled scene populates (padding slots keep their bind-time rows)
+    const int groups = std::max(1, (std::min(S_, max_scene_agents_) + OBS_WARPS - 1) / OBS_WARPS);
     k_obs<<<W_ * groups, OBS_BLOCK, sizeof(ObsSmem), stream_>>>(d_scenes_, st_, ex_, params_, S_, groups,
                                                                 opt_knn_idx_, key_thr_);
     if (prof) { GD_CUDA(cudaEventRecord(ev[2], stream_)); prof_pending_++; }

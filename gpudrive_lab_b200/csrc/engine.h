@@ -170,6 +170,7 @@ private:
     std::vector<void *> arena_slabs_;
     size_t arena_off_ = 0, arena_cap_ = 0;
     int max_roads_ = 0;        // over the pool
+    int max_scene_agents_ = 0; // over the pool: k_obs launches CTAs for these slots only
     Exports ex_{};
     StateDev st_{};
     std::vector<void *> owned_;

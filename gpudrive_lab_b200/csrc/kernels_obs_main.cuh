@@ -196,6 +196,8 @@ k_obs(const SceneDev *__restrict__ scenes, StateDev st, Exports ex, Params prm, 
             const bool narrow = apart && w < 3.f;
             if (apart && (outside || (narrow && !some))) pmg = 0;
             const int lo = narrow ? lo2 : 0, hi = narrow ? hi2 : NRAY - 1;
+            // (measured and dropped: the angular span of the rectangle's corners instead of the circle's -
+            //  four more atan2 per group cost more than the skipped groups save, 7.62 vs 7.40 ms)
             const bool keep = nearg || pmg != 0;
             const int e = (int)(__float_as_uint(dmin) >> 23) - 127;           // floor(log2(dmin))
             const int band = obs_band_of(dmin, e);
