@@ -157,7 +157,26 @@ int Engine::uploadScene(const SceneData &s, const std::string &key) {
     std::vector<int> coll;
     for (int r = 0; r < R; r++)
         if (s.rtype[r] == ET_RoadEdge || s.rtype[r] == ET_StopSign) coll.push_back(r);
-    const int C = (int)coll.size(), Cpad = (C + 31) & ~31;
+    {   // spatial order (Morton code of the 1 m quantised position): k_agents tests 32 consecutive boxes per
+        // bounding circle; collision results are flags, so the order of the table is free
+        float minx = 3e38f, miny = 3e38f;
+        for (int r : coll) { minx = std::min(minx, s.rx[r]); miny = std::min(miny, s.ry[r]); }
+        auto spread = [](uint32_t v) {
+            uint64_t x = v & 0xffffu;
+            x = (x | (x << 8)) & 0x00ff00ffull; x = (x | (x << 4)) & 0x0f0f0f0full;
+            x = (x | (x << 2)) & 0x33333333ull; x = (x | (x << 1)) & 0x55555555ull;
+            return x;
+        };
+        std::vector<std::pair<uint64_t, int>> keys;
+        for (int r : coll) {
+            const uint32_t qx = (uint32_t)std::min(65535.f, std::max(0.f, s.rx[r] - minx));
+            const uint32_t qy = (uint32_t)std::min(65535.f, std::max(0.f, s.ry[r] - miny));
+            keys.push_back({spread(qx) | (spread(qy) << 1), r});
+        }
+        std::sort(keys.begin(), keys.end());
+        for (size_t i = 0; i < keys.size(); i++) coll[i] = keys[i].second;
+    }
+    const int C = (int)coll.size(), Cpad = (C + 31) & ~31, CG = Cpad / 32;
 
     SceneDev dev;
     memset(&dev, 0, sizeof(dev));
@@ -212,6 +231,7 @@ int Engine::uploadScene(const SceneData &s, const std::string &key) {
     const size_t o_ra = section(sizeof(float4) * Rpad), o_rb = section(sizeof(float2) * Rpad),
                  o_rc = section(sizeof(uint32_t) * Rpad), o_rd = section(sizeof(float4) * Rpad),
                  o_cc = section(sizeof(float4) * Cpad), o_co = section(sizeof(float4) * 4 * Cpad),
+                 o_cg = section(sizeof(float4) * std::max(CG, 1)),
                  o_tr = section(sizeof(float) * (size_t)A * kTrajSize), o_aa = section(sizeof(float4) * A),
                  o_ab = section(sizeof(float4) * A), o_ac = section(sizeof(float4) * A),
                  o_me = section(sizeof(int4) * A);
@@ -320,6 +340,24 @@ int Engine::uploadScene(const SceneData &s, const std::string &key) {
         cc[i] = make_float4(px, py, rad, (float)s.rtype[r]);
     }
     for (int i = C; i < Cpad; i++) cc[i] = make_float4(1e30f, 1e30f, 0.f, 0.f);
+    {   // one circle per 32 consecutive collidable boxes, around their bounding circles
+        float4 *cg = F4(o_cg);
+        for (int g = 0; g < CG; g++) {
+            float lox = 3e38f, loy = 3e38f, hix = -3e38f, hiy = -3e38f;
+            const int n = std::min(32, C - g * 32);
+            for (int k = 0; k < n; k++) {
+                const float4 c = cc[g * 32 + k];
+                lox = std::min(lox, c.x); hix = std::max(hix, c.x); loy = std::min(loy, c.y); hiy = std::max(hiy, c.y);
+            }
+            const float gx = 0.5f * (lox + hix), gy = 0.5f * (loy + hiy);
+            float rad = 0.f;
+            for (int k = 0; k < n; k++) {
+                const float4 c = cc[g * 32 + k];
+                rad = std::max(rad, sqrtf((c.x - gx) * (c.x - gx) + (c.y - gy) * (c.y - gy)) + c.z);
+            }
+            cg[g] = n > 0 ? make_float4(gx, gy, rad * 1.0001f + 1e-3f, 0.f) : make_float4(1e30f, 1e30f, 0.f, 0.f);
+        }
+    }
     if (A) memcpy(blob.data() + o_tr, s.traj.data(), sizeof(float) * (size_t)A * kTrajSize);
     for (int a = 0; a < A; a++) {
         aa[a] = make_float4(s.vsize[a * 3], s.vsize[a * 3 + 1], s.vsize[a * 3 + 2], (float)s.id[a]);
@@ -341,6 +379,8 @@ int Engine::uploadScene(const SceneData &s, const std::string &key) {
     dev.numGroups = G;
     dev.coll_cull = reinterpret_cast<const float4 *>(base + o_cc);
     dev.coll_obb = reinterpret_cast<const float4 *>(base + o_co);
+    dev.coll_grp = reinterpret_cast<const float4 *>(base + o_cg);
+    dev.numCollGroups = CG;
     dev.traj = reinterpret_cast<const float *>(base + o_tr);
     dev.ag_a = reinterpret_cast<const float4 *>(base + o_aa);
     dev.ag_b = reinterpret_cast<const float4 *>(base + o_ab);

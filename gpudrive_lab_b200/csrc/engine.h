@@ -31,6 +31,8 @@ struct SceneDev {
     const float4 *s_d;        // [G*32] d2, yaw(heading), id, mapType
     const float4 *grp;        // [G][2] bounds of the group's boxes: circle cx, cy, r | z-class bit mask, then the
                               //        rectangle around the same centre: axis ux, uy, half extents a, b
+    // collidable road boxes (RoadEdge, StopSign) in spatial order, 32 per bounding circle:
+    const float4 *coll_grp;   // [Cpad/32] cx, cy, r around the bounding circles of the 32 boxes
     const float4 *coll_cull;  // [Cpad] cx, cy, bounding radius, type
     const float4 *coll_obb;   // [Cpad*4] corners(8) | axes(4) | origin(2) z dz
     const float *traj;        // [A][1456]
@@ -41,7 +43,7 @@ struct SceneDev {
     float zc_z[kMaxZClasses];   // distinct (z, d2) pairs of the road entities
     float zc_d2[kMaxZClasses];
     int32_t numZClasses;
-    int32_t numRoads, numAgents, numColl, numGroups;
+    int32_t numRoads, numAgents, numColl, numGroups, numCollGroups;
     float mean[3];
     int32_t mapName[32];
     int32_t scenarioId[32];

@@ -211,8 +211,17 @@ k_agents(const SceneDev *__restrict__ scenes, StateDev st, Exports ex, Params pr
             }
             // agent x static road boxes (edges + stop signs); Static agents never pair with them
             if (!(me.flags & AB_STATIC)) {
-                const int C = sc.numColl;
-                for (int j = lane; j < C; j += 32) {
+                // one lane per bounding circle of 32 boxes, then the boxes of the circles the agent reaches
+                const int CG = sc.numCollGroups;
+                for (int gbase = 0; gbase < CG; gbase += 32) {
+                  bool reach = false;
+                  if (gbase + lane < CG) {
+                      const float4 gc = sc.coll_grp[gbase + lane];
+                      const float gx = me.cx - gc.x, gy = me.cy - gc.y, gr = me.rad + gc.z;
+                      reach = gx * gx + gy * gy <= gr * gr;
+                  }
+                  for (unsigned gm = __ballot_sync(0xffffffffu, reach); gm; gm &= gm - 1) {
+                    const int j = (gbase + __ffs(gm) - 1) * 32 + lane;
                     const float4 cu = sc.coll_cull[j];
                     float dx = me.cx - cu.x, dy = me.cy - cu.y, rr = me.rad + cu.z;
                     if (dx * dx + dy * dy > rr * rr) continue;
@@ -230,6 +239,7 @@ k_agents(const SceneDev *__restrict__ scenes, StateDev st, Exports ex, Params pr
                     rb.org[0] = q3.x; rb.org[1] = q3.y;
                     if (!obb_collided(me.obb, rb)) continue;
                     hit_bits |= collide_info_bit(rtype);
+                  }
                 }
             }
         }
