@@ -149,7 +149,7 @@ __device__ __forceinline__ float ray_box_exact(float ox, float oy, float bx, flo
         const float denom = sgn * ((k < 2) ? ldx : ldy);
         const float neg_dist = __fsub_rn(1.f, sgn * ((k < 2) ? lox : loy));
         const bool par = denom == 0.0f;
-        const float t = __fdiv_rn(neg_dist, denom);
+        const float t = __fdiv_rn(neg_dist, par ? 1.f : denom);      // (a zero operand takes the division's slow path)
         miss = miss || (par && neg_dist < 0.0f);
         const bool enter = !par && denom < 0.0f && t >= tfirst;
         const bool leave = !par && denom > 0.0f && t <= tlast;
@@ -187,30 +187,50 @@ __device__ __forceinline__ bool ray_range(float a, float w, int &lo, int &hi) {
 // Returns false if none, else the ray index range [lo, hi]. (relx, rely): box centre relative to the ray
 // origin; (cphi, sphi): box axis. Written without early exits: in a warp some lane needs every step anyway,
 // and straight-line code with selects is cheaper than the divergence bookkeeping of the branches.
-__device__ __forceinline__ bool lidar_consider(const LidarCtx &c, float relx, float rely, float cphi, float sphi,
-                                               float d0, float d1, int &lo, int &hi)
+struct BoxCull {      // first half of lidar_consider: the cheap tests, and what the second half reuses
+    float fx, fy, maxcross, mindot;
+    bool close_box, alive;
+};
+
+__device__ __forceinline__ BoxCull lidar_cull(const LidarCtx &c, float relx, float rely, float cphi, float sphi,
+                                              float d0, float d1)
 {
+    BoxCull r;
     const float rbound = d0 + d1;                         // >= half diagonal
     const float D2 = fmaf(relx, relx, rely * rely);
     const float range = kLidarDistance + rbound;
     const bool in_range = D2 <= range * range;
-    const float fx = fmaf(c.fc, relx, c.fs * rely), fy = fmaf(c.fc, rely, -(c.fs * relx));   // centre in the fan frame
+    r.fx = fmaf(c.fc, relx, c.fs * rely); r.fy = fmaf(c.fc, rely, -(c.fs * relx));   // centre in the fan frame
     // box half axes e0 = d0 (cphi, sphi), e1 = d1 (-sphi, cphi)
     const float along = fmaf(relx, cphi, rely * sphi), across = fmaf(rely, cphi, -(relx * sphi));
-    const float maxcross = fmaf(d0, fabsf(across), d1 * fabsf(along));
-    const float mindot = D2 - fmaf(d0, fabsf(along), d1 * fabsf(across));
-    const bool close_box = !(mindot > 1e-6f * D2) || D2 <= (rbound + 0.01f) * (rbound + 0.01f);
+    r.maxcross = fmaf(d0, fabsf(across), d1 * fabsf(along));
+    r.mindot = D2 - fmaf(d0, fabsf(along), d1 * fabsf(across));
+    r.close_box = !(r.mindot > 1e-6f * D2) || D2 <= (rbound + 0.01f) * (rbound + 0.01f);
     const float cH = 0.5146014f, sH = 0.8574295f;     // cos / sin of 24.5 * delta + 4e-3 (fan half angle)
-    const bool outside = fx < -rbound                                  // behind the fan
-                         || fmaf(cH, fy, -(sH * fx)) > rbound           // beyond the last ray
-                         || fmaf(cH, fy, sH * fx) < -rbound;            // before the first ray
-    const float w = maxcross * rcp_fast(mindot);      // tan of the half width; atan(w) <= w
+    const bool outside = r.fx < -rbound                                  // behind the fan
+                         || fmaf(cH, r.fy, -(sH * r.fx)) > rbound         // beyond the last ray
+                         || fmaf(cH, r.fy, sH * r.fx) < -rbound;          // before the first ray
+    r.alive = in_range && (r.close_box || !outside);
+    return r;
+}
+
+// second half: the ray index range of a box that passed lidar_cull
+__device__ __forceinline__ bool lidar_range(const BoxCull &b, int &lo, int &hi)
+{
+    const float w = b.maxcross * rcp_fast(b.mindot);      // tan of the half width; atan(w) <= w
     int lo2, hi2;
-    const bool some = ray_range(fast_atan2(fy, fx), w * 1.0001f + 2e-3f, lo2, hi2);
-    const bool narrow = !close_box && w < 1.0f;
+    const bool some = ray_range(fast_atan2(b.fy, b.fx), w * 1.0001f + 2e-3f, lo2, hi2);
+    const bool narrow = !b.close_box && w < 1.0f;
     lo = narrow ? lo2 : 0;
     hi = narrow ? hi2 : NRAY - 1;
-    return in_range && (close_box || (!outside && (!narrow || some)));
+    return b.alive && (!narrow || some);
+}
+
+__device__ __forceinline__ bool lidar_consider(const LidarCtx &c, float relx, float rely, float cphi, float sphi,
+                                               float d0, float d1, int &lo, int &hi)
+{
+    const BoxCull b = lidar_cull(c, relx, rely, cphi, sphi, d0, d1);
+    return lidar_range(b, lo, hi);
 }
 
 // z-slab membership of the three lidar planes for a hull with object-space z in [zmin_obj, zmax_obj]
@@ -222,7 +242,10 @@ __device__ __forceinline__ int plane_mask(float pz, float bz, float d2, float zm
 #pragma unroll
     for (int p = 0; p < 3; p++) {
         const float oz = __fadd_rn(pz, offs[p]);
-        const float lz = __fdiv_rn(__fsub_rn(oz, bz), d2);
+        // 0 / d2 is 0, but a zero operand sends IEEE division down its slow path - and a plane at exactly the
+        // box's height is the common case (1 + 0.1 - 1.1), so it is special-cased
+        const float num = __fsub_rn(oz, bz);
+        const float lz = num == 0.f ? 0.f : __fdiv_rn(num == 0.f ? 1.f : num, d2);
         const bool in = !(__fsub_rn(zmax_obj, lz) < 0.f) && !(__fsub_rn(lz, zmin_obj) < 0.f);
         m |= in ? (1 << p) : 0;
     }

@@ -115,8 +115,9 @@ k_obs(const SceneDev *__restrict__ scenes, StateDev st, Exports ex, Params prm, 
         rotate_xy(qw, qz, 1.f, 0.f, rgx, rgy);     // rot.rotateVec(math::right)
         rotate_xy(qw, qz, 0.f, 1.f, fwx, fwy);     // rot.rotateVec(math::fwd)
         for (int i = lane; i < NRAY; i += 32) {
-            const float theta = __fadd_rn(__fmul_rn(kLidarAngle,
-                __fsub_rn(__fdiv_rn(2.f * (float)i, (float)NRAY), 1.f)), head);
+            // (ray 0: 0 / NRAY = 0 without the slow path IEEE division takes for a zero operand)
+            const float frac = i == 0 ? 0.f : __fdiv_rn(i == 0 ? 1.f : 2.f * (float)i, (float)NRAY);
+            const float theta = __fadd_rn(__fmul_rn(kLidarAngle, __fsub_rn(frac, 1.f)), head);
             // sim.cpp:411-412. Observation output with a 1e-5 bar, not agent state: CUDA's sincosf (<= 2 ulp
             // from glibc's cosf / sinf) instead of the bit-exact restatement, which costs four times as much.
             float x, y;
@@ -227,6 +228,9 @@ k_obs(const SceneDev *__restrict__ scenes, StateDev st, Exports ex, Params prm, 
                 const int li = base + lane;
                 const uint32_t desc = li < nlist ? wp.v.g.glist[li] : 0u;
                 const bool mine = li < nlist && (int)((desc >> 12) & 7u) == band;
+#ifndef GD_OBS_NO_CHUNK_SKIP
+                if (!__any_sync(FULL, mine)) continue;       // no group of this band in this chunk of the list
+#endif
                 const int pmg = (int)(desc >> 28);
                 const bool lid = mine && pmg != 0 &&
                     (ray_bits((desc >> 15) & 63u, (desc >> 21) & 63u) & open_for(open, pmg)) != 0ull;
@@ -265,13 +269,17 @@ k_obs(const SceneDev *__restrict__ scenes, StateDev st, Exports ex, Params prm, 
                         const int pm = (zmask_classes >> (3 * (int)(c & 0xffu))) & 7;
                         const float relx = ra.x - px, rely = ra.y - py;
                         const float cphi = 1.f - 2.f * ra.w * ra.w, sphi = 2.f * ra.z * ra.w;
-                        int lo, hi;
-                        const bool some = lidar_consider(lc, relx, rely, cphi, sphi, rb.x, rb.y, lo, hi);
-                        // trim the range to its first / last open ray (closed rays inside are clipped too)
-                        const unsigned long long m = (pm && some) ? (ray_bits(lo, hi) & open_for(open, pm)) : 0ull;
-                        lo = m ? __ffsll((long long)m) - 1 : 0;
-                        const int n = m ? 64 - __clzll((long long)m) - lo : 0;
-                        lidar_expand(wp, lane, lo, n, pm, (unsigned)e, relx, rely, cphi, sphi, rb.x, rb.y);
+                        // cheap tests first: about one pass in five has no box left after them
+                        const BoxCull bc = lidar_cull(lc, relx, rely, cphi, sphi, rb.x, rb.y);
+                        if (__any_sync(FULL, pm != 0 && bc.alive)) {
+                            int lo, hi;
+                            const bool some = lidar_range(bc, lo, hi);
+                            // trim the range to its first / last open ray (closed rays inside are clipped too)
+                            const unsigned long long m = (pm && some) ? (ray_bits(lo, hi) & open_for(open, pm)) : 0ull;
+                            lo = m ? __ffsll((long long)m) - 1 : 0;
+                            const int n = m ? 64 - __clzll((long long)m) - lo : 0;
+                            lidar_expand(wp, lane, lo, n, pm, (unsigned)e, relx, rely, cphi, sphi, rb.x, rb.y);
+                        }
                     }
                 }
             }
