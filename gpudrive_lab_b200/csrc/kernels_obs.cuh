@@ -161,6 +161,28 @@ __device__ __forceinline__ float ray_box_exact(float ox, float oy, float bx, flo
     return (entered && !miss) ? tfirst : -1.f;
 }
 
+// The exported depth of a ray whose winning box is already known: the reference's arithmetic for the one face
+// that decides it. A hit's depth is the largest entry parameter over the entering faces (broadphase.cpp:817-845
+// keeps the later, larger t); the slab with the larger entry is chosen with cheap arithmetic, then that face's
+// t is computed exactly as the reference does (rotate, divide origin and direction by the scale, IEEE division),
+// so the result has the reference's rounding. If the two entries tie within rounding, either face's t is the
+// depth to ~1e-7. Three IEEE divisions instead of the eight of the full restatement above.
+__device__ __forceinline__ float ray_box_exact_depth(float ox, float oy, float bx, float by, float qw, float qz,
+                                                     float d0, float d1, float dirx, float diry)
+{
+    float lox, loy, ldx, ldy;
+    inv_rotate_xy(qw, qz, __fsub_rn(ox, bx), __fsub_rn(oy, by), lox, loy);
+    inv_rotate_xy(qw, qz, dirx, diry, ldx, ldy);
+    const float ex = (-copysignf(d0, ldx) - lox) * rcp_fast(ldx);      // entry parameters, unscaled box frame
+    const float ey = (-copysignf(d1, ldy) - loy) * rcp_fast(ldy);
+    const bool use_x = ex > ey;                                        // (ties and NaNs go to y, like the reference's order)
+    const float sc = use_x ? d0 : d1;
+    const float slo = __fdiv_rn(use_x ? lox : loy, sc), sld = __fdiv_rn(use_x ? ldx : ldy, sc);
+    const float sgn = sld < 0.f ? 1.f : -1.f;                          // the entering face of the axis: denom < 0
+    const float denom = sgn * sld, neg_dist = __fsub_rn(1.f, sgn * slo);
+    return denom == 0.f ? -1.f : __fdiv_rn(neg_dist, denom);
+}
+
 // atan2 with |error| < 2e-4 rad (odd minimax polynomial on [0, 1] + octant folding)
 __device__ __forceinline__ float fast_atan2(float y, float x) {
     const float ax = fabsf(x), ay = fabsf(y);

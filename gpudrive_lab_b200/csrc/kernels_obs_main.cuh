@@ -309,7 +309,11 @@ k_obs(const SceneDev *__restrict__ scenes, StateDev st, Exports ex, Params prm, 
                     type = (int)((__ldg(&sc.s_c[id]) >> 8) & 0xffu);
                 }
                 const float2 d = wp.v.g.raydir[i % NRAY];
+#ifdef GD_OBS_FULL_EXACT
                 const float te = ray_box_exact(px, py, bx, by, bqw, bqz, d0, d1, d.x, d.y);
+#else
+                const float te = ray_box_exact_depth(px, py, bx, by, bqw, bqz, d0, d1, d.x, d.y);
+#endif
                 if (te >= 0.f) t = te;      // (a grazing ray may flip to a miss in exact arithmetic: keep the fast t)
                 const float2 xy = wp.v.g.rayxy[i % NRAY];
                 v = make_float4(t, (float)type, __fmul_rn(t, xy.x), __fmul_rn(t, xy.y));
