@@ -20,7 +20,7 @@ lib.gd_debug_counters(out, 1)
 sim.step()
 lib.gd_debug_counters(out, 0)
 n = out[0]
-names = ["agents", "groups listed", "groups processed", " with lidar", " with knn", "items pushed", "push calls", "sum max popcount/push",
-         "in-radius candidates", "drain rounds", "overflow agents", "wide boxes", "items drained"]
+names = ["agents", "groups listed", "groups processed", " with lidar", " with knn", "(box, ray) pairs clipped", "clip-stage calls",
+         "-", "in-radius candidates", "clip rounds", "agents over the candidate cap"]
 for i, nm in enumerate(names):
     print(f"{nm:28s} {out[i]:12d}  per agent {out[i] / max(n, 1):9.2f}")
