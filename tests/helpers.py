@@ -286,3 +286,25 @@ class EngineAdapter:
 
     def reset(self, worlds):
         self.sim.reset(list(worlds))
+
+
+def ragged_scenes(out_dir):
+    """Edge-case scenarios cut from a synthetic one: one agent with three short polylines; two agents with only
+    a stop sign and one road edge; three agents and no road at all. Returns their paths."""
+    import json
+    from gpudrive_lab_b200 import synth
+    base = synth.make_scenario(3, num_agents=6)
+    none = {"sdc_track_index": 0, "objects_of_interest": [], "tracks_to_predict": []}
+    a = dict(base, objects=base["objects"][:1], metadata=none,
+             roads=[r for r in base["roads"] if r["type"] in ("lane", "road_edge")][:3])
+    b = dict(base, objects=base["objects"][:2],
+             roads=[r for r in base["roads"] if r["type"] == "stop_sign"][:1] +
+                   [r for r in base["roads"] if r["type"] == "road_edge"][:1])
+    c = dict(base, objects=base["objects"][:3], roads=[])
+    paths = []
+    for name, s in (("one_agent", a), ("two_roads", b), ("no_roads", c)):
+        p = os.path.join(str(out_dir), f"ragged_{name}.json")
+        with open(p, "w") as fh:
+            json.dump(s, fh)
+        paths.append(p)
+    return paths

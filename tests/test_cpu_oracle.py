@@ -112,3 +112,26 @@ def test_bev_matches_reference_live(tmp_path):
         mgr.set_actions(a)
         ref.step(); mgr.step()
     ref.close()
+
+
+def test_ragged_and_empty_scenes_match_reference(tmp_path):
+    """Edge cases: a single agent, a map of two entities, a map with no road at all - lidar, k-nearest padding and
+    partner rows of the restatement against the unmodified reference."""
+    from helpers import ragged_scenes
+    from oracle import refmgr
+    if not refmgr.available():
+        pytest.skip("oracle/_ref not built")
+    scenes = ragged_scenes(tmp_path)
+    for model in (0, 2):
+        pd = param_dict(dynamicsModel=model, enableLidar=True)
+        ref = refmgr.RefManager(scenes, ref_params(pd))
+        orc = _make(scenes, pd)
+        assert ref.tensor("shape")[:, 1].tolist()[2] == 0
+        stats = {}
+        for t in range(6):
+            a = random_actions(t, len(scenes), 128, model)
+            ref.tensor("action")[...] = a
+            orc.set_actions(a)
+            ref.step(); orc.step()
+            compare_step(snapshot_ref(ref), kat._snapshot(orc, TENSORS_CMP), 50.0, True, tag=f"model {model} step {t + 1}",
+                         stats=stats)

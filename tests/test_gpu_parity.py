@@ -165,3 +165,12 @@ def test_auto_reset_rollout_from_device_pool(synth_dir):
             compare_step(snapshot_ref(ref, TENSORS_CMP + ["map_observation", "expert_trajectory"]),
                          snapshot_engine(sim, TENSORS_CMP + ["map_observation", "expert_trajectory"]),
                          50.0, False, tag=f"after re-bind at {t + 1}", stats=stats)
+
+
+def test_ragged_and_empty_scenes(tmp_path):
+    """One agent; a map of two entities; a map with no road at all (empty road table, empty collidable table,
+    no lidar hit on the road planes, all-padding road-map rows)."""
+    from helpers import ragged_scenes
+    scenes = ragged_scenes(tmp_path)
+    for model in (0, 2):
+        run_parity(scenes, param_dict(dynamicsModel=model, enableLidar=True), 12)
