@@ -26,8 +26,8 @@ sys.path.insert(0, ROOT)
 
 TOTAL_WORLDS = 8192
 # dram__bytes_read.sum + dram__bytes_write.sum of one k_obs launch of the default workload, from the committed
-# ncu capture profiles/r01_v11_k_obs_raw.txt (87.7 MB read + 7.420 GB written)
-K_OBS_DRAM_BYTES_PER_LAUNCH = 7.508e9
+# ncu capture profiles/r01_v13_k_obs_raw.txt (88.9 MB read + 7.421 GB written)
+K_OBS_DRAM_BYTES_PER_LAUNCH = 7.509e9
 AGENTS = 64
 SLOTS = 128               # consts::kMaxAgentCount of the reference -> identical tensor shapes
 UNIQUE_SCENES = 64        # distinct synthetic scenarios, cycled over the worlds
@@ -344,7 +344,7 @@ def main_engine(args):
             "roofline": {"bound": "hbm", "kernel": "k_obs", "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": achieved / peak, "peak_source": peak_src,
                          "traffic": K_OBS_DRAM_BYTES_PER_LAUNCH if (world_size == 1 and total_worlds == TOTAL_WORLDS) else None,
-                         "traffic_source": "profiles/r01_v11_k_obs_raw.txt (ncu --set full: dram__bytes_read.sum + dram__bytes_write.sum)",
+                         "traffic_source": "profiles/r01_v13_k_obs_raw.txt (ncu --set full: dram__bytes_read.sum + dram__bytes_write.sum)",
                          "bytes_per_agent_step": b_obs, "agent_steps_per_launch": n_live,
                          "avg_launch_ms": obs_ms, "k_agents_avg_ms": agents_ms,
                          "step_bytes_per_agent_step": b_step,
