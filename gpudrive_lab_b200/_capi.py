@@ -46,7 +46,7 @@ class GdRewardShaping(C.Structure):
 class GdStats(C.Structure):
     _fields_ = [(n, C.c_uint64) for n in (
         "steps", "agent_steps", "controlled_steps", "episodes_reset", "collided_road",
-        "collided_vehicle", "collided_nonvehicle", "goals_reached", "dones")]
+        "collided_vehicle", "collided_nonvehicle", "goals_reached", "dones", "sat_tests")]
 
 
 class GdSceneInfo(C.Structure):
@@ -60,7 +60,7 @@ EXPORTED_SYMBOLS = [
     "gd_delete_agents", "gd_tensor", "gd_step_host", "gd_pool_add", "gd_bind_worlds", "gd_stats",
     "gd_num_worlds", "gd_max_agents", "gd_launch_count", "gd_stream", "gd_last_error",
     "gd_scene_info", "gd_scene_tensors", "gd_scene_road_pose", "gd_policy_obs", "gd_set_option", "gd_kernel_times",
-    "gd_pool_convert", "gd_pool_count", "gd_shaped_reward", "gd_expert_actions",
+    "gd_pool_convert", "gd_pool_count", "gd_shaped_reward", "gd_expert_actions", "gd_auto_reset_pool", "gd_auto_reset",
 ]
 
 TENSOR_IDS = {
@@ -98,6 +98,8 @@ def load():
     lib.gd_step_host.argtypes = [H, C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p]
     lib.gd_pool_add.argtypes = [H, C.c_char_p, C.POINTER(C.c_int32)]
     lib.gd_bind_worlds.argtypes = [H, C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.c_int32]
+    lib.gd_auto_reset_pool.argtypes = [H, C.POINTER(C.c_int32), C.c_int32]
+    lib.gd_auto_reset.argtypes = [H]
     lib.gd_shaped_reward.argtypes = [H, C.POINTER(GdRewardShaping), C.POINTER(GdTensorDesc)]
     lib.gd_expert_actions.argtypes = [H, C.POINTER(GdTensorDesc)]
     lib.gd_pool_convert.argtypes = [C.POINTER(C.c_char_p), C.c_int32, C.c_float, C.c_char_p, C.c_int32]

@@ -89,6 +89,9 @@ int gd_bind_worlds(GdHandle h, const int32_t *worlds, const int32_t *scene_ids, 
     GD_TRY({ E(h)->bindWorlds(worlds, scene_ids, n); })
 }
 
+int gd_auto_reset_pool(GdHandle h, const int32_t *scene_ids, int32_t n) { GD_TRY({ E(h)->autoResetPool(scene_ids, n); }) }
+int gd_auto_reset(GdHandle h) { GD_TRY({ E(h)->autoReset(); }) }
+
 int gd_shaped_reward(GdHandle h, const GdRewardShaping *cfg, GdTensorDesc *out) {
     GD_TRY({
         gd::TensorDesc d = E(h)->shapedReward(cfg->mode, cfg->collision_weight, cfg->goal_achieved_weight,

@@ -50,10 +50,16 @@ Engine::Engine(int gpu_id, int max_agents, const Params &params, const std::vect
         throw std::runtime_error("gpudrive_b200: no CUDA device visible; this engine has no CPU fallback");
     if (gpu_ < 0 || gpu_ >= ndev) throw std::runtime_error("gpu_id out of range");
     GD_CUDA(cudaSetDevice(gpu_));
-    GD_CUDA(cudaStreamCreateWithFlags(&stream_, cudaStreamNonBlocking));
-    GD_CUDA(cudaStreamCreateWithFlags(&copy_stream_, cudaStreamNonBlocking));
+    // Blocking streams, like Madrona's (external/madrona/include/madrona/cuda_utils.inl:62): work the caller
+    // enqueued on the legacy default stream - torch's `action_tensor().to_torch()[...] = a` - is ordered before
+    // the step, and the caller's later reads on that stream after it. Callers on other non-blocking streams
+    // order themselves against gd_stream().
+    GD_CUDA(cudaStreamCreate(&stream_));
+    GD_CUDA(cudaStreamCreate(&copy_stream_));
     GD_CUDA(cudaEventCreateWithFlags(&ev_agents_, cudaEventDisableTiming));
     GD_CUDA(cudaEventCreateWithFlags(&ev_copied_, cudaEventDisableTiming));
+    GD_CUDA(cudaEventCreateWithFlags(&ev_worklist_, cudaEventDisableTiming));
+    GD_CUDA(cudaMallocHost(&h_worklist_, sizeof(int32_t) * 2 * (size_t)W_));
 
     allocExports();
 
@@ -87,10 +93,14 @@ Engine::Engine(int gpu_id, int max_agents, const Params &params, const std::vect
 Engine::~Engine() {
     cudaSetDevice(gpu_);
     cudaDeviceSynchronize();
+    destroyStepGraph();
     for (auto &e : prof_ev_) cudaEventDestroy(e);
+    if (h_worklist_) cudaFreeHost(h_worklist_);
+    if (ev_worklist_) cudaEventDestroy(ev_worklist_);
     for (void *p : owned_) cudaFree(p);
     for (void *p : arena_slabs_) cudaFree(p);
     if (d_scenes_) cudaFree(d_scenes_);
+    if (d_pool_ids_) cudaFree(d_pool_ids_);
     if (h_pinned_actions_) cudaFreeHost(h_pinned_actions_);
     if (ev_agents_) cudaEventDestroy(ev_agents_);
     if (ev_copied_) cudaEventDestroy(ev_copied_);
@@ -129,7 +139,7 @@ void Engine::allocExports() {
     st_.world_scene = devAlloc<int32_t>(owned_, W_);
     st_.reset_flag = devAlloc<int32_t>(owned_, W_);
     st_.stats = devAlloc<unsigned long long>(owned_, 16);
-    d_worklist_ = devAlloc<int32_t>(owned_, W_);
+    d_worklist_ = devAlloc<int32_t>(owned_, 2 * (size_t)W_);
     d_act_stage_ = devAlloc<float>(owned_, (size_t)W_ * S_ * kActionSize);
 }
 
@@ -434,11 +444,19 @@ void Engine::syncSceneTable() {
     scene_table_dirty_ = false;
 }
 
-void Engine::launchBindReset(const std::vector<int32_t> &worlds, bool rebind) {
+void Engine::launchBindReset(const std::vector<int32_t> &worlds, bool rebind, bool scene_ids_uploaded) {
     if (worlds.empty()) return;
     syncSceneTable();
     const int n = (int)worlds.size();
-    GD_CUDA(cudaMemcpyAsync(d_worklist_, worlds.data(), n * sizeof(int32_t), cudaMemcpyHostToDevice, stream_));
+    // pinned staging: wait only until the previous list has left the buffer, not for the device to drain
+    GD_CUDA(cudaEventSynchronize(ev_worklist_));
+    memcpy(h_worklist_, worlds.data(), n * sizeof(int32_t));
+    GD_CUDA(cudaMemcpyAsync(d_worklist_, h_worklist_, n * sizeof(int32_t), cudaMemcpyHostToDevice, stream_));
+    GD_CUDA(cudaEventRecord(ev_worklist_, stream_));
+    if (scene_ids_uploaded) {
+        k_set_scene<<<(n + 255) / 256, 256, 0, stream_>>>(d_worklist_, d_worklist_ + W_, n, st_.world_scene);
+        launches_++;
+    }
     if (rebind) {
         k_bind<<<dim3(n, BIND_SPLIT), 256, 0, stream_>>>(d_worklist_, d_scenes_, st_, ex_, S_);
         launches_++;
@@ -447,37 +465,105 @@ void Engine::launchBindReset(const std::vector<int32_t> &worlds, bool rebind) {
     k_reset<<<n, blk, 0, stream_>>>(d_worklist_, d_scenes_, st_, ex_, S_, params_.dynamicsModel);
     launches_++;
     GD_CUDA(cudaGetLastError());
-    // the pageable worklist buffer must stay alive until the copy is consumed
-    GD_CUDA(cudaStreamSynchronize(stream_));
     episodes_reset_ += n;
 }
 
+int Engine::obsGroups() const {
+    // CTAs only for slots some pooled scene populates (padding slots keep their bind-time rows)
+    return std::max(1, (std::min(S_, max_scene_agents_) + OBS_WARPS - 1) / OBS_WARPS);
+}
+
+void Engine::destroyStepGraph() {
+    if (graph_exec_) cudaGraphExecDestroy(graph_exec_);
+    if (graph_) cudaGraphDestroy(graph_);
+    graph_exec_ = nullptr; graph_ = nullptr;
+    graph_key_ = StepGraphKey();
+}
+
+// One step as one graph launch (the reference's GPU backend launches its step graph the same way,
+// external/madrona/src/mw/cuda_exec.cpp:1699,1891): [ev0] k_agents [ev1 | ev_agents] k_obs [ev2] (k_bev).
+// Built node by node rather than by stream capture, so nothing the caller does on other streams meanwhile can
+// invalidate it. The profiling events are re-pointed at the ring slot before every launch.
+void Engine::buildStepGraph(const StepGraphKey &key) {
+    destroyStepGraph();
+    GD_CUDA(cudaGraphCreate(&graph_, 0));
+    cudaGraphNode_t last = nullptr;
+    auto dep = [&]() { return last ? &last : nullptr; };
+    auto ndep = [&]() { return last ? (size_t)1 : (size_t)0; };
+    auto add_event = [&](cudaEvent_t ev, cudaGraphNode_t *keep) {
+        cudaGraphNode_t n;
+        GD_CUDA(cudaGraphAddEventRecordNode(&n, graph_, dep(), ndep(), ev));
+        if (keep) *keep = n;
+        last = n;
+    };
+    auto add_kernel = [&](void *fn, dim3 grid, dim3 block, size_t smem, void **args) {
+        cudaKernelNodeParams kp = {};
+        kp.func = fn; kp.gridDim = grid; kp.blockDim = block; kp.sharedMemBytes = (unsigned)smem;
+        kp.kernelParams = args; kp.extra = nullptr;
+        cudaGraphNode_t n;
+        GD_CUDA(cudaGraphAddKernelNode(&n, graph_, dep(), ndep(), &kp));
+        last = n;
+    };
+    const SceneDev *scenes = d_scenes_;
+    int S = S_, one = 1, zero = 0, groups = key.groups, knn = key.knn_idx;
+    float key_thr = key_thr_;
+    if (key.profile) add_event(prof_ev_[0], &graph_ev_nodes_[0]);
+    {
+        void *args[] = {&scenes, &st_, &ex_, &params_, &S, &one, &one, &zero};
+        add_kernel((void *)k_agents<AGENTS_BLOCK>, dim3(W_), dim3(AGENTS_BLOCK), sizeof(AgentBox) * (size_t)S_, args);
+    }
+    if (key.profile) add_event(prof_ev_[1], &graph_ev_nodes_[1]);
+    add_event(ev_agents_, nullptr);         // reward / done / info are final here (stepHost's copy stream waits on it)
+    {
+        void *args[] = {&scenes, &st_, &ex_, &params_, &S, &groups, &knn, &key_thr, &zero};
+        add_kernel((void *)k_obs, dim3(W_ * groups), dim3(OBS_BLOCK), sizeof(ObsSmem), args);
+    }
+    if (key.profile) add_event(prof_ev_[2], &graph_ev_nodes_[2]);
+    if (bev_enabled_) {
+        void *args[] = {&scenes, &st_, &ex_, &params_, &S, &key_thr};
+        add_kernel((void *)k_bev, dim3(W_ * S_), dim3(BEV_BLOCK), sizeof(BevSmem), args);
+    }
+    GD_CUDA(cudaGraphInstantiate(&graph_exec_, graph_, 0));
+    graph_key_ = key;
+}
+
 // setupRestOfTasks (src/sim.cpp:785-943): collisions, reward, (--t), done, observation fan-out
-void Engine::launchRest(bool decrement) {
+void Engine::launchRest(bool decrement, bool only_flagged) {
     syncSceneTable();
+    const int flagged = only_flagged ? 1 : 0;
     const size_t smem_agents = sizeof(AgentBox) * (size_t)S_;
     const bool prof = opt_profile_ && decrement;
+    const int groups = obsGroups();
+    kernels_per_step_ = bev_enabled_ ? 3 : 2;
     cudaEvent_t *ev = nullptr;
     if (prof) {
         if (prof_pending_ == kProfRing) foldProfile();
         ev = &prof_ev_[3 * prof_pending_];
-        GD_CUDA(cudaEventRecord(ev[0], stream_));
     }
+    if (decrement && opt_graph_) {
+        StepGraphKey key;
+        key.scenes = d_scenes_; key.groups = groups; key.knn_idx = opt_knn_idx_; key.profile = prof ? 1 : 0;
+        if (!graph_exec_ || !(key == graph_key_)) buildStepGraph(key);
+        if (prof) {
+            for (int i = 0; i < 3; i++)
+                GD_CUDA(cudaGraphExecEventRecordNodeSetEvent(graph_exec_, graph_ev_nodes_[i], ev[i]));
+            prof_pending_++;
+        }
+        GD_CUDA(cudaGraphLaunch(graph_exec_, stream_));
+        launches_ += kernels_per_step_;
+        return;
+    }
+    if (prof) GD_CUDA(cudaEventRecord(ev[0], stream_));
     k_agents<AGENTS_BLOCK><<<W_, AGENTS_BLOCK, smem_agents, stream_>>>(d_scenes_, st_, ex_, params_, S_,
-                                                                    decrement ? 1 : 0, decrement ? 1 : 0);
+                                                                    decrement ? 1 : 0, decrement ? 1 : 0, flagged);
     if (prof) GD_CUDA(cudaEventRecord(ev[1], stream_));
     if (mark_agents_done_) GD_CUDA(cudaEventRecord(ev_agents_, stream_));   // reward / done / info are final here
-    // CTAs only for slots some pooled scene populates (padding slots keep their bind-time rows)
-    const int groups = std::max(1, (std::min(S_, max_scene_agents_) + OBS_WARPS - 1) / OBS_WARPS);
     k_obs<<<W_ * groups, OBS_BLOCK, sizeof(ObsSmem), stream_>>>(d_scenes_, st_, ex_, params_, S_, groups,
-                                                                opt_knn_idx_, key_thr_);
+                                                                opt_knn_idx_, key_thr_, flagged);
     if (prof) { GD_CUDA(cudaEventRecord(ev[2], stream_)); prof_pending_++; }
-    launches_ += 2;
-    kernels_per_step_ = 2;
-    if (bev_enabled_) {
+    if (bev_enabled_)
         k_bev<<<W_ * S_, BEV_BLOCK, sizeof(BevSmem), stream_>>>(d_scenes_, st_, ex_, params_, S_, key_thr_);
-        launches_++; kernels_per_step_ = 3;
-    }
+    launches_ += kernels_per_step_;
     GD_CUDA(cudaGetLastError());
 }
 
@@ -496,8 +582,8 @@ void Engine::step() {
 
 void Engine::reset(const int32_t *worlds, int n) {
     GD_CUDA(cudaSetDevice(gpu_));
-    // python may have written tensors on another stream; reference semantics are fully synchronous
-    GD_CUDA(cudaDeviceSynchronize());
+    // (the engine stream is a blocking one: tensor writes the caller made on the legacy default stream are
+    //  already ordered before the kernels below, no device-wide synchronisation needed)
     std::vector<int32_t> list;
     for (int i = 0; i < n; i++) {
         if (worlds[i] < 0 || worlds[i] >= W_) throw std::runtime_error("reset: world index out of range");
@@ -513,7 +599,7 @@ void Engine::reset(const int32_t *worlds, int n) {
 void Engine::setMaps(const std::vector<std::string> &scenes) {
     if ((int)scenes.size() != W_) throw std::runtime_error("set_maps: len(maps) must equal num_worlds");
     GD_CUDA(cudaSetDevice(gpu_));
-    GD_CUDA(cudaDeviceSynchronize());
+    host_binding_stale_ = false;
     scene_paths_ = scenes;
     for (int w = 0; w < W_; w++) {
         deleted_[w].clear();                         // src/mgr.cpp:643-646
@@ -532,7 +618,7 @@ void Engine::deleteAgents(int world, const int32_t *ids, int n) {
     if (world < 0 || world >= W_) throw std::runtime_error("deleteAgents: world index out of range");
     if (n > S_) throw std::runtime_error("deleteAgents: more ids than agent slots");
     GD_CUDA(cudaSetDevice(gpu_));
-    GD_CUDA(cudaDeviceSynchronize());
+    refreshHostBinding();
     // src/mgr.cpp:698-709: ids overwrite the head of the world's DeletedAgents list
     std::vector<int32_t> cur(S_);
     GD_CUDA(cudaMemcpy(cur.data(), ex_.deleted + (size_t)world * S_, S_ * sizeof(int32_t), cudaMemcpyDeviceToHost));
@@ -560,19 +646,70 @@ int Engine::poolAdd(const std::string &path) {
 
 void Engine::bindWorlds(const int32_t *worlds, const int32_t *scene_ids, int n) {
     GD_CUDA(cudaSetDevice(gpu_));
-    GD_CUDA(cudaDeviceSynchronize());
+    refreshHostBinding();
     std::vector<int32_t> list;
     for (int i = 0; i < n; i++) {
         if (worlds[i] < 0 || worlds[i] >= W_) throw std::runtime_error("bind: world index out of range");
         if (scene_ids[i] < 0 || scene_ids[i] >= (int)scenes_.size()) throw std::runtime_error("bind: scene id out of range");
+    }
+    if (n > W_) throw std::runtime_error("bind: more entries than worlds");
+    for (int i = 0; i < n; i++) {
         world_scene_[worlds[i]] = scene_ids[i];
         scene_paths_[worlds[i]] = scenes_[scene_ids[i]].key;
         list.push_back(worlds[i]);
     }
-    GD_CUDA(cudaMemcpy(st_.world_scene, world_scene_.data(), W_ * sizeof(int32_t), cudaMemcpyHostToDevice));
-    launchBindReset(list, true);
+    if (n > 0) {
+        // the new binding travels with the work list (pinned, stream-ordered): no synchronous copy, no host stall
+        GD_CUDA(cudaEventSynchronize(ev_worklist_));
+        memcpy(h_worklist_ + W_, scene_ids, n * sizeof(int32_t));
+        GD_CUDA(cudaMemcpyAsync(d_worklist_ + W_, h_worklist_ + W_, n * sizeof(int32_t), cudaMemcpyHostToDevice, stream_));
+        launchBindReset(list, true, /*scene_ids_uploaded=*/true);
+    }
     launchRest(false);
     sync();
+}
+
+void Engine::autoResetPool(const int32_t *scene_ids, int n) {
+    GD_CUDA(cudaSetDevice(gpu_));
+    if (n <= 0) throw std::runtime_error("auto_reset_pool: empty pool");
+    for (int i = 0; i < n; i++)
+        if (scene_ids[i] < 0 || scene_ids[i] >= (int)scenes_.size()) throw std::runtime_error("auto_reset_pool: scene id out of range");
+    GD_CUDA(cudaStreamSynchronize(stream_));
+    if (d_pool_ids_) GD_CUDA(cudaFree(d_pool_ids_));
+    GD_CUDA(cudaMalloc(&d_pool_ids_, sizeof(int32_t) * (size_t)n));
+    GD_CUDA(cudaMemcpy(d_pool_ids_, scene_ids, sizeof(int32_t) * (size_t)n, cudaMemcpyHostToDevice));
+    if (!d_pool_cursor_) d_pool_cursor_ = devAlloc<int32_t>(owned_, W_);
+    std::vector<int32_t> cur(W_);
+    for (int w = 0; w < W_; w++) cur[w] = w % n;        // world w starts at pool entry w % n
+    GD_CUDA(cudaMemcpy(d_pool_cursor_, cur.data(), sizeof(int32_t) * (size_t)W_, cudaMemcpyHostToDevice));
+    n_pool_ = n;
+}
+
+void Engine::autoReset() {
+    GD_CUDA(cudaSetDevice(gpu_));
+    if (!n_pool_) throw std::runtime_error("auto_reset: call auto_reset_pool first");
+    syncSceneTable();
+    k_autoreset_select<<<(W_ * 32 + 255) / 256, 256, 0, stream_>>>(st_, ex_, d_scenes_, d_pool_ids_, n_pool_,
+                                                                    d_pool_cursor_, W_, S_);
+    k_bind<<<dim3(W_, BIND_SPLIT), 256, 0, stream_>>>(nullptr, d_scenes_, st_, ex_, S_);
+    const int blk = ((S_ + 31) / 32) * 32;
+    k_reset<<<W_, blk, 0, stream_>>>(nullptr, d_scenes_, st_, ex_, S_, params_.dynamicsModel);
+    launches_ += 3;
+    launchRest(false, true);      // the Reset graph's rest-of-step, for the flagged worlds only
+    GD_CUDA(cudaGetLastError());
+    host_binding_stale_ = true;
+}
+
+void Engine::refreshHostBinding() {
+    if (!host_binding_stale_) return;
+    GD_CUDA(cudaMemcpyAsync(world_scene_.data(), st_.world_scene, W_ * sizeof(int32_t), cudaMemcpyDeviceToHost, stream_));
+    GD_CUDA(cudaStreamSynchronize(stream_));
+    for (int w = 0; w < W_; w++) {
+        const std::string &key = scenes_[world_scene_[w]].key;
+        scene_paths_[w] = key.substr(0, key.find("#del"));
+        if (key.find("#del") == std::string::npos) deleted_[w].clear();
+    }
+    host_binding_stale_ = false;
 }
 
 void Engine::stepHost(const float *actions, int action_cols, float *reward, int32_t *done, int32_t *info) {
@@ -606,7 +743,7 @@ TensorDesc Engine::policyObs(int normalize) {
     k_policy_obs<<<W_ * S_, 256, 0, stream_>>>(ex_, d_policy_obs_, S_, normalize ? 1 : 0);
     launches_++;
     GD_CUDA(cudaGetLastError());
-    GD_CUDA(cudaStreamSynchronize(stream_));
+    if (!opt_async_aux_) GD_CUDA(cudaStreamSynchronize(stream_));
     TensorDesc d{};
     d.ptr = d_policy_obs_; d.dtype = 0; d.ndim = 3; d.shape[0] = W_; d.shape[1] = S_; d.shape[2] = width; d.device = gpu_;
     return d;
@@ -623,7 +760,7 @@ TensorDesc Engine::shapedReward(int mode, float collision_w, float goal_w, float
     k_shaped_reward<<<(n + 255) / 256, 256, 0, stream_>>>(ex_, a, d_shaped_reward_, W_, S_);
     launches_++;
     GD_CUDA(cudaGetLastError());
-    GD_CUDA(cudaStreamSynchronize(stream_));
+    if (!opt_async_aux_) GD_CUDA(cudaStreamSynchronize(stream_));
     TensorDesc d{};
     d.ptr = d_shaped_reward_; d.dtype = 0; d.ndim = 2; d.shape[0] = W_; d.shape[1] = S_; d.device = gpu_;
     return d;
@@ -637,7 +774,7 @@ TensorDesc Engine::expertActions() {
     k_expert_actions<<<(unsigned)((n + 255) / 256), 256, 0, stream_>>>(ex_, d_expert_actions_, n, params_.dynamicsModel);
     launches_++;
     GD_CUDA(cudaGetLastError());
-    GD_CUDA(cudaStreamSynchronize(stream_));
+    if (!opt_async_aux_) GD_CUDA(cudaStreamSynchronize(stream_));
     TensorDesc d{};
     d.ptr = d_expert_actions_; d.dtype = 0; d.ndim = 4; d.shape[0] = W_; d.shape[1] = S_; d.shape[2] = kTrajLen;
     d.shape[3] = cols; d.device = gpu_;
@@ -654,7 +791,9 @@ void Engine::setOption(int option, int value) {
         }
         if (value && !opt_profile_) { prof_pending_ = 0; prof_agents_ms_ = prof_obs_ms_ = 0; prof_steps_ = 0; }
         opt_profile_ = value ? 1 : 0;
-    } else throw std::runtime_error("unknown option");
+    } else if (option == 2) opt_graph_ = value ? 1 : 0;
+    else if (option == 3) opt_async_aux_ = value ? 1 : 0;
+    else throw std::runtime_error("unknown option");
 }
 
 void Engine::foldProfile() {
@@ -677,17 +816,22 @@ void Engine::kernelTimes(double *agents_ms, double *obs_ms, int64_t *steps) {
 }
 
 StepStats Engine::stats() {
+    GD_CUDA(cudaSetDevice(gpu_));
     StepStats s;
     memset(&s, 0, sizeof(s));
+    unsigned long long dev[ST_NUM];
+    GD_CUDA(cudaMemcpyAsync(dev, st_.stats, sizeof(dev), cudaMemcpyDeviceToHost, stream_));
+    GD_CUDA(cudaStreamSynchronize(stream_));
     s.steps = steps_;
-    s.episodes_reset = episodes_reset_;
-    uint64_t live = 0, ctrl = 0;
-    for (int w = 0; w < W_; w++) {
-        live += scenes_[world_scene_[w]].numAgents;
-        ctrl += scenes_[world_scene_[w]].numControlled;
-    }
-    s.agent_steps = live * steps_;          // exact while the world->scene binding is unchanged
-    s.controlled_steps = ctrl * steps_;
+    s.episodes_reset = episodes_reset_ + dev[ST_AUTO_RESETS];
+    s.agent_steps = dev[ST_AGENT_STEPS];
+    s.controlled_steps = dev[ST_CONTROLLED_STEPS];
+    s.collided_road = dev[ST_COLLIDED_ROAD];
+    s.collided_vehicle = dev[ST_COLLIDED_VEHICLE];
+    s.collided_nonvehicle = dev[ST_COLLIDED_NONVEHICLE];
+    s.goals_reached = dev[ST_GOALS_REACHED];
+    s.dones = dev[ST_DONES];
+    s.sat_tests = dev[ST_SAT_TESTS];
     return s;
 }
 

@@ -83,7 +83,13 @@ struct StateDev {
     int32_t *collided;    // [W,S] CollisionDetectionEvent.hasCollided
     int32_t *world_scene; // [W]
     int32_t *reset_flag;  // [W]
-    unsigned long long *stats; // [16] episode statistics accumulators
+    unsigned long long *stats; // [16] episode statistics accumulators (StatSlot), written by k_agents
+};
+
+// slots of StateDev::stats
+enum StatSlot : int {
+    ST_AGENT_STEPS = 0, ST_CONTROLLED_STEPS, ST_COLLIDED_ROAD, ST_COLLIDED_VEHICLE, ST_COLLIDED_NONVEHICLE,
+    ST_GOALS_REACHED, ST_DONES, ST_AUTO_RESETS, ST_SAT_TESTS, ST_NUM
 };
 
 enum TensorId : int32_t {
@@ -100,12 +106,14 @@ struct TensorDesc {
     int32_t device;
 };
 
-struct StepStats {      // gd_stats
+struct StepStats {      // gd_stats; everything but `steps` is accumulated on the device by k_agents
     uint64_t steps;
     uint64_t agent_steps;       // live agents x steps
     uint64_t controlled_steps;  // live controlled agents x steps
-    uint64_t episodes_reset;
+    uint64_t episodes_reset;    // worlds reset (reset / set_maps / bind_worlds / auto_reset), the ctor's included
+    // (agent, step) pairs at which Info.collidedWith* / Info.reachedGoal / Done went 0 -> 1 (src/sim.cpp:597-626,713-724)
     uint64_t collided_road, collided_vehicle, collided_nonvehicle, goals_reached, dones;
+    uint64_t sat_tests;         // two-sided OBB separating-axis tests evaluated (candidates that survived the cheap rejects)
 };
 
 class Engine {
@@ -125,6 +133,9 @@ public:
     // scenario pool (device auto-reset)
     int poolAdd(const std::string &path);       // returns scene id
     void bindWorlds(const int32_t *worlds, const int32_t *scene_ids, int n);   // + reset
+    // device-side auto-reset: finished worlds move on to the next scenario of the pool, without the host
+    void autoResetPool(const int32_t *scene_ids, int n);
+    void autoReset();
     StepStats stats();
     // flat normalised policy observation (GPUDriveTorchEnv.get_obs) computed from the current exports
     TensorDesc policyObs(int normalize);
@@ -132,7 +143,9 @@ public:
     TensorDesc shapedReward(int mode, float collision_w, float goal_w, float off_road_w, float log_dist_w,
                             const float *agent_weights, const int32_t *world_time_steps);
     TensorDesc expertActions();
-    // options: 0 = write the knn index side buffer (default 1), 1 = per-kernel CUDA-event timing (default 0)
+    // options: 0 = write the knn index side buffer (default 1), 1 = per-kernel CUDA-event timing (default 0),
+    // 2 = launch a step as one CUDA graph (default 1), 3 = policy_obs / shaped_reward / expert_actions return
+    // without waiting for the device (default 0: they return when the tensor is ready)
     void setOption(int option, int value);
     // accumulated device time of the two step kernels since profiling was switched on (ms) and the step count
     void kernelTimes(double *agents_ms, double *obs_ms, int64_t *steps);
@@ -152,8 +165,8 @@ private:
     int uploadScene(const SceneData &s, const std::string &key);
     void *arenaAlloc(size_t bytes);
     void syncSceneTable();
-    void launchBindReset(const std::vector<int32_t> &worlds, bool rebind);
-    void launchRest(bool decrement);
+    void launchBindReset(const std::vector<int32_t> &worlds, bool rebind, bool scene_ids_uploaded = false);
+    void launchRest(bool decrement, bool only_flagged = false);
     void allocExports();
 
     int gpu_, W_, S_;
@@ -177,6 +190,12 @@ private:
     StateDev st_{};
     std::vector<void *> owned_;
     int32_t *d_worklist_ = nullptr;   // [W] scratch for reset lists
+    int32_t *d_pool_ids_ = nullptr, *d_pool_cursor_ = nullptr;   // auto-reset pool and the per-world cursor into it
+    int n_pool_ = 0;
+    bool host_binding_stale_ = false;   // auto-reset re-bound worlds on the device: world_scene_ needs a read-back
+    void refreshHostBinding();
+    int32_t *h_worklist_ = nullptr;   // [W] pinned staging of the reset lists (stream-ordered upload)
+    cudaEvent_t ev_worklist_ = nullptr;   // the last upload from h_worklist_ has been consumed
     float *h_pinned_actions_ = nullptr;
     float *d_shaped_reward_ = nullptr;    // [W,S], allocated on first use
     float *d_expert_actions_ = nullptr;   // [W,S,91,3 or 10], allocated on first use
@@ -188,7 +207,21 @@ private:
     int kernels_per_step_ = 0;
     uint64_t launches_ = 0;
     uint64_t steps_ = 0, episodes_reset_ = 0;
-    int opt_knn_idx_ = 1, opt_profile_ = 0;
+    int opt_knn_idx_ = 1, opt_profile_ = 0, opt_graph_ = 1, opt_async_aux_ = 0;
+    // one step = one graph launch: [ev] k_agents [ev] k_obs [ev] (k_bev); rebuilt when a launch parameter changes
+    struct StepGraphKey {
+        const void *scenes = nullptr; int groups = -1, knn_idx = -1, profile = -1;
+        bool operator==(const StepGraphKey &o) const {
+            return scenes == o.scenes && groups == o.groups && knn_idx == o.knn_idx && profile == o.profile;
+        }
+    };
+    StepGraphKey graph_key_;
+    cudaGraph_t graph_ = nullptr;
+    cudaGraphExec_t graph_exec_ = nullptr;
+    cudaGraphNode_t graph_ev_nodes_[3] = {nullptr, nullptr, nullptr};
+    void buildStepGraph(const StepGraphKey &key);
+    void destroyStepGraph();
+    int obsGroups() const;
     float key_thr_ = 0.f;
     static constexpr int kProfRing = 64;
     std::vector<cudaEvent_t> prof_ev_;      // 3 events per ring slot

@@ -11,6 +11,11 @@
 // The instruction order below was read from the disassembly of this image's libm.so.6 and is
 // pinned by tests/test_cpu_trig.py (bit-equality with libm over 2^24+ inputs).
 // Valid for |x| < 120; callers fall back to fp64 sin/cos beyond that (never hit: |yaw| <= 2*pi).
+//
+// Attribution: the algorithm and the coefficient tables are glibc's (GNU C Library 2.39, LGPL-2.1-or-later,
+// Copyright (C) Free Software Foundation, Inc.), which took them from ARM's optimized-routines
+// (Copyright (c) Arm Limited, MIT OR Apache-2.0 WITH LLVM-exception). Third-party arithmetic restated for
+// bit-parity; it is not code of the reference repository.
 #pragma once
 #include <cmath>
 #include <cstdint>

@@ -13,10 +13,12 @@
 //     reference's operation order, so the selected SET is bit-exact.
 //   lidar: groups are visited in bands of increasing distance. Before each band the rays that are still
 //     "open" (no hit closer than the band) are gathered into one bit mask per plane; a group, and then a
-//     box, is skipped with one AND if the rays its angular range covers are all closed. Surviving
-//     (box, ray) pairs go through a per-warp shared-memory queue so 32 lanes clip rays in lock step; the
-//     closest hit per ray is kept with a 64-bit shared atomicMin of (t, box). Winners are re-clipped with
-//     the reference's exact object-space arithmetic at the end.
+//     box, is skipped with one AND if the rays its angular range covers are all closed. The warp expands the
+//     surviving (box, ray range) pairs of a pass into (box, ray) pairs, 32 per round, one per lane (prefix sum
+//     + owner search over shuffles: no queue), so 32 lanes clip rays in lock step; the closest hit per ray is
+//     kept with a native 32-bit shared atomicMin on the bits of t, the box id written by the lane that holds
+//     the minimum. At write-out the deciding face of each winner is evaluated with the reference's exact
+//     object-space arithmetic, so exported depths carry its rounding.
 #pragma once
 #include "device_math.cuh"
 #include "engine.h"
@@ -62,7 +64,7 @@ struct ObsWarpSmem {
             uint32_t bt[3 * NRAY];            // lidar: bits of the closest hit distance per plane and ray (none: ~0)
             uint16_t bid[3 * NRAY];           // and its box: sorted road slot, or 0x4000 | agent slot
         } l;
-        float stage[32 * 9];                  // row transpose buffer for coalesced stores
+        float stage[32 * 9 + 4];              // row transpose buffer for coalesced stores (+ up to 3 floats of misalignment)
     } u;
     union {                                   // the histogram is only needed after the lidar is written out
         struct {
@@ -352,22 +354,33 @@ __device__ __forceinline__ void open_rays(const uint32_t *best, float dist, int 
 }
 
 
-// Emit `m` rows held one per lane (lanes with has_row) to consecutive global rows starting at dst,
-// via the per-warp transpose buffer. rank = exclusive prefix of has_row.
+// Emit `m` rows held one per lane (lanes with has_row) to consecutive global rows starting at dst, via the
+// per-warp transpose buffer. rank = exclusive prefix of has_row. dst is only 4-byte aligned in general (a row is
+// 36 bytes): the rows are staged `mis` = (float index of dst) & 3 floats into the buffer, so that shared and global
+// addresses are congruent modulo 16 bytes and everything but the <= 3 floats in front of the first and behind the
+// last 16-byte boundary moves as LDS.128 / STG.128 (72 vector stores per 32 rows instead of 288 scalar ones).
+__device__ __forceinline__ void flush_aligned(const float *stage, float *dst, int mis, int n, int lane)
+{
+    const int head = min((4 - mis) & 3, n);
+    if (lane < head) dst[lane] = stage[mis + lane];
+    const int nq = (n - head) >> 2;
+    const float4 *s4 = reinterpret_cast<const float4 *>(stage + mis + head);
+    float4 *d4 = reinterpret_cast<float4 *>(dst + head);
+    for (int i = lane; i < nq; i += 32) d4[i] = s4[i];
+    const int t0 = head + 4 * nq;
+    if (lane < n - t0) dst[t0 + lane] = stage[mis + t0 + lane];
+}
+
 __device__ __forceinline__ void flush_rows(float *stage, float *dst, const float (&row)[9], bool has_row,
                                            int rank, int m, int lane)
 {
+    const int mis = (int)((reinterpret_cast<uintptr_t>(dst) >> 2) & 3u);
     if (has_row) {
 #pragma unroll
-        for (int k = 0; k < 9; k++) stage[rank * 9 + k] = row[k];
+        for (int k = 0; k < 9; k++) stage[mis + rank * 9 + k] = row[k];
     }
     __syncwarp();
-    const int n = m * 9;
-#pragma unroll
-    for (int k = 0; k < 9; k++) {
-        const int i = lane + 32 * k;
-        if (i < n) dst[i] = stage[i];
-    }
+    flush_aligned(stage, dst, mis, m * 9, lane);
     __syncwarp();
 }
 

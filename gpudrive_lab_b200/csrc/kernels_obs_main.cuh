@@ -12,15 +12,16 @@ namespace gd {
 // reference's `length() <= radius` (knn.hpp:88, sim.cpp:268-271) without a square root per entity.
 __global__ void __launch_bounds__(OBS_BLOCK, GD_OBS_MINB)
 k_obs(const SceneDev *__restrict__ scenes, StateDev st, Exports ex, Params prm, int S, int groups,
-      int write_knn_idx, float key_thr)
+      int write_knn_idx, float key_thr, int only_flagged)
 {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     ObsSmem &sm = *reinterpret_cast<ObsSmem *>(smem_raw);
 
     const int w = blockIdx.x / groups;
     const int g = blockIdx.x % groups;
+    if (only_flagged && !st.reset_flag[w]) return;      // auto-reset: only the worlds that were just re-bound
     const SceneDev &sc = scenes[st.world_scene[w]];
-    const int A = sc.numAgents, R = sc.numRoads;
+    const int A = sc.numAgents;
     if (g * OBS_WARPS >= A) return;
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -75,13 +76,13 @@ k_obs(const SceneDev *__restrict__ scenes, StateDev st, Exports ex, Params prm, 
     if (active && classical) {
         const int P = S - 1;
         float *dstbase = ex.partner_obs + wa * P * kPartnerObsSize;
+        bool const_staged = false;
         for (int base = 0; base < P; base += 32) {
-            const int jp = base + lane;
-            const bool has = jp < P;
-            float row[9];
-            row[0] = row[1] = row[2] = row[3] = row[4] = row[5] = row[6] = row[7] = 0.f;
-            row[8] = -2.f;                                            // zero_nonexist()
+            const int m = min(32, P - base);
+            float *dst = dstbase + (size_t)base * 9;
             if (base < A - 1) {       // (warp-uniform) straight-line inside: some lane takes each path anyway
+                const int jp = base + lane;
+                const bool has = jp < P;
                 const bool exists = has && jp < A - 1;
                 const int j = exists ? (jp < a ? jp : jp + 1) : 0;   // OtherAgents order, level_gen.cpp:450-464
                 const float4 o0 = sm.a0[j], o1 = sm.a1[j];
@@ -90,15 +91,27 @@ k_obs(const SceneDev *__restrict__ scenes, StateDev st, Exports ex, Params prm, 
                 inv_rotate_xy(qw, qz, __fsub_rn(o0.x, px), __fsub_rn(o0.y, py), rx, ry);
                 inv_mul_quat(qw, qz, o0.z, o0.w, rw, rz);
                 const bool seen = exists && !(__fsqrt_rn(len2_xy(rx, ry)) > radius);
+                float row[9];
                 row[0] = seen ? o1.y : 0.f; row[1] = seen ? rx : 0.f; row[2] = seen ? ry : 0.f;
                 row[3] = seen ? quat_to_yaw(rw, rz) : 0.f;
                 row[4] = seen ? o3.x : 0.f; row[5] = seen ? o3.y : 0.f; row[6] = seen ? o3.z : 0.f;
                 row[7] = seen ? o1.z : 0.f;
-                row[8] = seen ? o1.w : (exists ? -1.f : -2.f);       // PartnerObservation::zero()
+                row[8] = seen ? o1.w : (exists ? -1.f : -2.f);       // PartnerObservation::zero() / zero_nonexist()
+                flush_rows(wp.u.stage, dst, row, has, lane, m, lane);
+            } else {
+                // every row of the chunk is zero_nonexist(); chunks start 1152 bytes apart, so the staged image
+                // (and its alignment) is the same for all of them: stage it once
+                const int mis = (int)((reinterpret_cast<uintptr_t>(dst) >> 2) & 3u);
+                if (!const_staged) {
+#pragma unroll
+                    for (int k = 0; k < 9; k++) wp.u.stage[mis + lane * 9 + k] = k == 8 ? -2.f : 0.f;
+                    __syncwarp();
+                    const_staged = true;
+                }
+                flush_aligned(wp.u.stage, dst, mis, m * 9, lane);
             }
-            const int m = min(32, P - base);
-            flush_rows(wp.u.stage, dstbase + (size_t)base * 9, row, has, lane, m, lane);
         }
+        __syncwarp();
     }
 
     // ------------------------------------------------------------ lidar set-up
@@ -485,45 +498,111 @@ k_obs(const SceneDev *__restrict__ scenes, StateDev st, Exports ex, Params prm, 
         }
     }
 
-    // emission (candidate order: by distance band, then by sorted slot)
-    for (int base = 0; base < N && emitted < K; base += 32) {
-        const int i = base + lane;
-        bool acc = false; int e = 0; unsigned kb = 0;
+    // One chunk of 32 candidates: is entry i selected, and which sorted slot / road word does it carry?
+    auto candidate = [&](int i, int &e, uint32_t &rc) -> bool {
+        bool acc = false; unsigned kb = 0;
+        e = 0;
         if (i < N) {
             if (overflow) { e = i; acc = slot_key(i, kb); }
             else { acc = true; kb = wp.ckey[i]; e = wp.cpos[i]; }
         }
-        uint32_t rc = 0;
-        if (acc) rc = __ldg(&sc.s_c[e]);
+        rc = acc ? __ldg(&sc.s_c[e]) : 0u;
         if (!take_all) acc = acc && (kb < thr || (kb == thr && (rc >> 16) <= idx_thr));
-        const unsigned am = __ballot_sync(FULL, acc);
-        int rank = __popc(am & lt_mask);
-        int m = __popc(am);
-        if (emitted + m > K) { m = K - emitted; if (rank >= m) acc = false; }
-        float row[9];
-        {   // straight-line (most lanes of a chunk emit a row; e is a valid slot on the others)
-            const float4 ra = __ldg(&sc.s_a[e]); const float2 rb = __ldg(&sc.s_b[e]);
-            const float4 rd = __ldg(&sc.s_d[e]);
-            float ox, oy, rw, rz;
-            inv_rotate_xy(qw, qz, __fsub_rn(ra.x, px), __fsub_rn(ra.y, py), ox, oy);
-            inv_mul_quat(qw, qz, ra.z, ra.w, rw, rz);
-            row[0] = ox; row[1] = oy; row[2] = rb.x; row[3] = rb.y; row[4] = rd.x;
-            row[5] = quat_to_yaw(rw, rz); row[6] = (float)((rc >> 8) & 0xffu); row[7] = rd.z; row[8] = rd.w;
-            if (acc && write_knn_idx) kidx[emitted + rank] = (int32_t)(rc >> 16);
+        return acc;
+    };
+    auto make_row = [&](int e, uint32_t rc, float (&row)[9]) {
+        // straight-line (most lanes of a chunk emit a row; e is a valid slot on the others)
+        const float4 ra = __ldg(&sc.s_a[e]); const float2 rb = __ldg(&sc.s_b[e]);
+        const float4 rd = __ldg(&sc.s_d[e]);
+        float ox, oy, rw, rz;
+        inv_rotate_xy(qw, qz, __fsub_rn(ra.x, px), __fsub_rn(ra.y, py), ox, oy);
+        inv_mul_quat(qw, qz, ra.z, ra.w, rw, rz);
+        row[0] = ox; row[1] = oy; row[2] = rb.x; row[3] = rb.y; row[4] = rd.x;
+        row[5] = quat_to_yaw(rw, rz); row[6] = (float)((rc >> 8) & 0xffu); row[7] = rd.z; row[8] = rd.w;
+    };
+
+    if (first_k_only) {
+        // Linear algorithm: the reference emits the first K in-radius entities in road-index order
+        // (sim.cpp:261-279), so the order is part of the contract. The selected road indices go into a bit map
+        // (<= 10 000 bits, in the dead group-list / ray buffers); a row's position is the number of selected
+        // indices below its own: one popc after a per-word prefix.
+        constexpr int BMW = (kMaxRoadEntityCount + 31) / 32;        // 313 words
+        static_assert(sizeof(wp.v) >= BMW * 4, "bit map does not fit");
+        static_assert(sizeof(wp.u) >= 320 * 2, "prefix table does not fit");
+        uint32_t *bm = reinterpret_cast<uint32_t *>(&wp.v);
+        uint16_t *pre = reinterpret_cast<uint16_t *>(&wp.u);
+        __syncwarp();
+        for (int i = lane; i < BMW; i += 32) bm[i] = 0u;
+        __syncwarp();
+        for (int base = 0; base < N; base += 32) {
+            int e; uint32_t rc;
+            if (candidate(base + lane, e, rc)) atomicOr(&bm[rc >> 21], 1u << ((rc >> 16) & 31u));
         }
-        flush_rows(wp.u.stage, rows + (size_t)emitted * 9, row, acc, rank, m, lane);
-        emitted += m;
-    }
-    // padding rows: fillZeros (knn.hpp:19-28 -> id = 0, mapType = 0) for the k-nearest algorithm,
-    // MapObservation::zero() (id = -1, mapType = -1) for the linear one (sim.cpp:277-279)
-    {
-        const float padv = first_k_only ? -1.f : 0.f;
+        __syncwarp();
+        {   // exclusive prefix of the per-word counts: lane owns words [10 * lane, 10 * lane + 10)
+            unsigned sum = 0;
+#pragma unroll
+            for (int k = 0; k < 10; k++) { const int wi = lane * 10 + k; sum += wi < BMW ? __popc(bm[wi]) : 0; }
+            unsigned incl = sum;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const unsigned v = __shfl_up_sync(FULL, incl, o);
+                if (lane >= o) incl += v;
+            }
+            unsigned acc = incl - sum;
+#pragma unroll
+            for (int k = 0; k < 10; k++) {
+                const int wi = lane * 10 + k;
+                pre[wi] = (uint16_t)acc;
+                acc += wi < BMW ? __popc(bm[wi]) : 0;
+            }
+            emitted = min(K, (int)__shfl_sync(FULL, incl, 31));
+        }
+        __syncwarp();
+        for (int base = 0; base < N; base += 32) {
+            int e; uint32_t rc;
+            const bool acc = candidate(base + lane, e, rc);
+            float row[9];
+            make_row(e, rc, row);
+            const unsigned idx = rc >> 16;
+            const int pos = (int)pre[idx >> 5] + __popc(bm[idx >> 5] & ((1u << (idx & 31u)) - 1u));
+            if (acc && pos < K) {
+#pragma unroll
+                for (int k = 0; k < 9; k++) rows[(size_t)pos * 9 + k] = row[k];
+                if (write_knn_idx) kidx[pos] = (int32_t)idx;
+            }
+        }
+        // padding rows: MapObservation::zero() (id = -1, mapType = -1), sim.cpp:277-279
         const int n = (K - emitted) * 9;
         float *dst = rows + (size_t)emitted * 9;
-        for (int i = lane; i < n; i += 32) dst[i] = (i % 9) >= 7 ? padv : 0.f;
-        if (write_knn_idx)
-            for (int i = emitted + lane; i < K; i += 32) kidx[i] = -1;
+        for (int i = lane; i < n; i += 32) dst[i] = (i % 9) >= 7 ? -1.f : 0.f;
+    } else {
+        // k-nearest: the reference leaves the rows in heap order; here by distance band, then by sorted slot
+        for (int base = 0; base < N && emitted < K; base += 32) {
+            int e; uint32_t rc;
+            bool acc = candidate(base + lane, e, rc);
+            const unsigned am = __ballot_sync(FULL, acc);
+            const int rank = __popc(am & lt_mask);
+            int m = __popc(am);
+            if (emitted + m > K) { m = K - emitted; if (rank >= m) acc = false; }
+            float row[9];
+            make_row(e, rc, row);
+            if (acc && write_knn_idx) kidx[emitted + rank] = (int32_t)(rc >> 16);
+            flush_rows(wp.u.stage, rows + (size_t)emitted * 9, row, acc, rank, m, lane);
+            emitted += m;
+        }
+        // padding rows: fillZeros (knn.hpp:19-28 -> all zero, id = 0, mapType = 0). An agent's block of rows is
+        // 16-byte aligned (7 200 bytes per agent): <= 3 scalar zeros up to the boundary, then STG.128
+        const int n = (K - emitted) * 9;
+        float *dst = rows + (size_t)emitted * 9;
+        const int head = min((4 - ((emitted * 9) & 3)) & 3, n);
+        if (lane < head) dst[lane] = 0.f;
+        float4 *d4 = reinterpret_cast<float4 *>(dst + head);
+        const int nq = (n - head) >> 2;              // (K * 9 is a multiple of 4: no tail)
+        for (int i = lane; i < nq; i += 32) d4[i] = make_float4(0.f, 0.f, 0.f, 0.f);
     }
+    if (write_knn_idx)
+        for (int i = emitted + lane; i < K; i += 32) kidx[i] = -1;
 }
 
 } // namespace gd

@@ -17,12 +17,16 @@ __global__ void __launch_bounds__(256)
 k_bind(const int32_t *__restrict__ worlds, const SceneDev *__restrict__ scenes, StateDev st,
        Exports ex, int S)
 {
-    const int w = worlds[blockIdx.x];
+    // explicit work list, or (worlds == nullptr, auto-reset) every world whose reset flag is set
+    const int w = worlds ? worlds[blockIdx.x] : (int)blockIdx.x;
+    if (!worlds && !st.reset_flag[w]) return;
     const SceneDev &sc = scenes[st.world_scene[w]];
     const int A = sc.numAgents, R = sc.numRoads;
     const int tid = blockIdx.y * blockDim.x + threadIdx.x;
     const int nthr = gridDim.y * blockDim.x;
 
+    if (!worlds)      // auto-reset binds pooled scenarios, which carry no deletions (set_maps clears the list too)
+        for (int a = tid; a < S; a += nthr) ex.deleted[(size_t)w * S + a] = -1;
     // expert trajectories: live rows from the pool, padding rows Trajectory::zero (types.hpp:357-367)
     {
         float4 *dst = reinterpret_cast<float4 *>(ex.traj + (size_t)w * S * kTrajSize);
@@ -122,7 +126,8 @@ k_bind(const int32_t *__restrict__ worlds, const SceneDev *__restrict__ scenes, 
 __global__ void k_reset(const int32_t *__restrict__ worlds, const SceneDev *__restrict__ scenes,
                         StateDev st, Exports ex, int S, int dynamicsModel)
 {
-    const int w = worlds[blockIdx.x];
+    const int w = worlds ? worlds[blockIdx.x] : (int)blockIdx.x;
+    if (!worlds && !st.reset_flag[w]) return;
     const SceneDev &sc = scenes[st.world_scene[w]];
     const int a = threadIdx.x;
     if (a >= sc.numAgents || a >= S) return;
@@ -151,6 +156,50 @@ __global__ void k_reset(const int32_t *__restrict__ worlds, const SceneDev *__re
     info[0] = info[1] = info[2] = info[3] = 0;
     info[4] = (int32_t)b.w;
     ex.response[wa] = resp;
+}
+
+// bind_worlds: the new world -> scene binding arrives with the work list
+__global__ void k_set_scene(const int32_t *__restrict__ worlds, const int32_t *__restrict__ scene_ids, int n,
+                            int32_t *__restrict__ world_scene)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) world_scene[worlds[i]] = scene_ids[i];
+}
+
+// Device-side auto-reset (gd_auto_reset): one warp per world. A world is finished when every controlled agent is
+// done (what gpudrive/env/env_puffer.py tests before it resets a world) - or, with no controlled agent, when the
+// episode has run out. A finished world moves on in the scenario pool: cursor' = (cursor + 1 + w % (n - 1)) % n,
+// is re-bound to pool[cursor'] and flagged; k_bind / k_reset / the rest-of-step kernels then run over the flagged
+// worlds only. No host round trip anywhere.
+__global__ void __launch_bounds__(256)
+k_autoreset_select(StateDev st, Exports ex, const SceneDev *__restrict__ scenes, const int32_t *__restrict__ pool,
+                   int n_pool, int32_t *__restrict__ cursor, int W, int S)
+{
+    const int w = (int)((blockIdx.x * blockDim.x + threadIdx.x) >> 5), lane = threadIdx.x & 31;
+    if (w >= W) return;
+    const int A = scenes[st.world_scene[w]].numAgents;
+    int ctrl = 0, pending = 0;
+    for (int a = lane; a < A; a += 32) {
+        const size_t wa = (size_t)w * S + a;
+        const int c = ex.controlled[wa];
+        ctrl += c ? 1 : 0;
+        pending += (c && ex.done[wa] != 1) ? 1 : 0;
+    }
+    ctrl = __reduce_add_sync(0xffffffffu, ctrl);
+    pending = __reduce_add_sync(0xffffffffu, pending);
+    const bool finished = ctrl > 0 ? pending == 0 : (A == 0 || ex.steps_remaining[(size_t)w * S] <= 0);
+    if (lane == 0) {
+        int flag = 0;
+        if (finished) {
+            const int cur = cursor[w];
+            const int nxt = n_pool > 1 ? (cur + 1 + w % (n_pool - 1)) % n_pool : 0;
+            cursor[w] = nxt;
+            st.world_scene[w] = pool[nxt];
+            flag = 1;
+            atomicAdd(&st.stats[ST_AUTO_RESETS], 1ull);
+        }
+        st.reset_flag[w] = flag;
+    }
 }
 
 // stepHost: contiguous [W*S, cols] host actions -> the first `cols` columns of the [W*S, 10] action rows

@@ -18,7 +18,7 @@ struct AgentBox {        // shared-memory record per agent slot, phase B
     int32_t flags;       // bit0 skip (invalid expert / done), bit1 static response, bit2 live
 };
 
-constexpr int AB_SKIP = 1, AB_STATIC = 2, AB_LIVE = 4;
+constexpr int AB_SKIP = 1, AB_STATIC = 2, AB_LIVE = 4, AB_DONE0 = 8;   // DONE0: Done was set when the step began
 
 // expandAABBWithMotion (broadphase.cpp:438-462) for one axis
 __device__ __forceinline__ void expand_axis(float v, float &lo, float &hi) {
@@ -52,12 +52,16 @@ __device__ __forceinline__ bool pair_ignored(int a, int b) {
 template <int BLOCK>
 __global__ void __launch_bounds__(BLOCK)
 k_agents(const SceneDev *__restrict__ scenes, StateDev st, Exports ex, Params prm, int S,
-         int decrement, int do_move)
+         int decrement, int do_move, int only_flagged)
 {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     AgentBox *box = reinterpret_cast<AgentBox *>(smem_raw);
+    // episode statistics of this world's step (gd_stats): 0 -> 1 transitions of the Info / Done flags
+    __shared__ unsigned s_cnt[ST_NUM];
+    if (threadIdx.x < ST_NUM) s_cnt[threadIdx.x] = 0;
 
     const int w = blockIdx.x;
+    if (only_flagged && !st.reset_flag[w]) return;      // auto-reset: only the worlds that were just re-bound
     const SceneDev &sc = scenes[st.world_scene[w]];
     const int A = sc.numAgents;
     const int tid = threadIdx.x;
@@ -71,6 +75,7 @@ k_agents(const SceneDev *__restrict__ scenes, StateDev st, Exports ex, Params pr
         float4 rv = st.rv[wa];
         int collided = st.collided[wa];
         int done = ex.done[wa];
+        const int done0 = done;
         const int resp = ex.response[wa];
         const int controlled = ex.controlled[wa];
         const int t = ex.steps_remaining[wa];
@@ -186,7 +191,7 @@ k_agents(const SceneDev *__restrict__ scenes, StateDev st, Exports ex, Params pr
         } else if (done && !collided) {
             skip = 1;
         }
-        bx.flags = AB_LIVE | (skip ? AB_SKIP : 0) | (resp == RT_Static ? AB_STATIC : 0);
+        bx.flags = AB_LIVE | (skip ? AB_SKIP : 0) | (resp == RT_Static ? AB_STATIC : 0) | (done0 ? AB_DONE0 : 0);
         st.collided[wa] = collided;
     }
     __syncthreads();
@@ -195,6 +200,7 @@ k_agents(const SceneDev *__restrict__ scenes, StateDev st, Exports ex, Params pr
     for (int a = warp; a < A; a += NWARP) {
         const AgentBox &me = box[a];
         int hit_bits = 0;
+        unsigned nsat = 0;
         if (!(me.flags & AB_SKIP)) {
             // agent x agent
             for (int j = lane; j < A; j += 32) {
@@ -205,6 +211,7 @@ k_agents(const SceneDev *__restrict__ scenes, StateDev st, Exports ex, Params pr
                 if (!(me.zlo < ot.zhi && ot.zlo < me.zhi)) continue;              // AABB::overlaps, strict
                 float dx = me.cx - ot.cx, dy = me.cy - ot.cy, rr = me.rad + ot.rad;
                 if (dx * dx + dy * dy > rr * rr) continue;
+                nsat++;
                 if (!obb_collided(me.obb, ot.obb)) continue;
                 if (pair_ignored(me.type, ot.type)) continue;
                 hit_bits |= collide_info_bit(ot.type);
@@ -237,6 +244,7 @@ k_agents(const SceneDev *__restrict__ scenes, StateDev st, Exports ex, Params pr
                     rb.cx[2] = q1.x; rb.cy[2] = q1.y; rb.cx[3] = q1.z; rb.cy[3] = q1.w;
                     rb.ax[0] = q2.x; rb.ay[0] = q2.y; rb.ax[1] = q2.z; rb.ay[1] = q2.w;
                     rb.org[0] = q3.x; rb.org[1] = q3.y;
+                    nsat++;
                     if (!obb_collided(me.obb, rb)) continue;
                     hit_bits |= collide_info_bit(rtype);
                   }
@@ -245,21 +253,30 @@ k_agents(const SceneDev *__restrict__ scenes, StateDev st, Exports ex, Params pr
         }
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) hit_bits |= __shfl_xor_sync(0xffffffffu, hit_bits, o);
+        if (decrement) {
+            nsat = __reduce_add_sync(0xffffffffu, nsat);
+            if (lane == 0 && nsat) atomicAdd(&s_cnt[ST_SAT_TESTS], nsat);
+        }
         if (lane == 0 && hit_bits) {
             const size_t wa = (size_t)w * S + a;
             st.collided[wa] = 1;
             int32_t *info = ex.info + wa * kInfoSize;
-            if (hit_bits & 1) info[0] = 1;
-            if (hit_bits & 2) info[1] = 1;
-            if (hit_bits & 4) info[2] = 1;
+#pragma unroll
+            for (int k = 0; k < 3; k++)
+                if (hit_bits & (1 << k)) {
+                    if (decrement && info[k] == 0) atomicAdd(&s_cnt[ST_COLLIDED_ROAD + k], 1u);
+                    info[k] = 1;
+                }
         }
     }
     __syncthreads();
 
     // ------------------------------------------------------------------ phase C: reward, --t, done
+    if (decrement && tid == 0) s_cnt[ST_AGENT_STEPS] = (unsigned)A;
     for (int a = tid; a < A; a += BLOCK) {
         const size_t wa = (size_t)w * S + a;
         const float4 agc = sc.ag_c[a];
+        if (decrement && ex.controlled[wa]) atomicAdd(&s_cnt[ST_CONTROLLED_STEPS], 1u);
         const float px = box[a].cx, py = box[a].cy;
         const float dxg = __fsub_rn(px, agc.x), dyg = __fsub_rn(py, agc.y);
         const float dist = __fsqrt_rn(len2_xy(dxg, dyg));
@@ -280,9 +297,17 @@ k_agents(const SceneDev *__restrict__ scenes, StateDev st, Exports ex, Params pr
             done = 1;
         }
         if (done != 1 || info[3] != 1) {
-            if (dist < prm.distanceToGoalThreshold) { done = 1; info[3] = 1; }
+            if (dist < prm.distanceToGoalThreshold) {
+                if (decrement && info[3] != 1) atomicAdd(&s_cnt[ST_GOALS_REACHED], 1u);
+                done = 1; info[3] = 1;
+            }
         }
+        if (decrement && done == 1 && !(box[a].flags & AB_DONE0)) atomicAdd(&s_cnt[ST_DONES], 1u);
         ex.done[wa] = done;
+    }
+    if (decrement) {
+        __syncthreads();
+        if (tid < ST_NUM && s_cnt[tid]) atomicAdd(&st.stats[tid], (unsigned long long)s_cnt[tid]);
     }
 }
 

@@ -9,9 +9,15 @@ Same names, argument meaning and tensor layouts as the reference. Differences, a
   * enable_batch_renderer=True, rgb_tensor(), depth_tensor() raise: no graphics stack on this box.
   * bev_observation_tensor() needs SimManager(..., enable_bev=True): the grid is 160 KB per agent slot,
     so it is opt-in here (the reference always computes it).
-  * agent_roadmap rows come in road-entity index order (the reference's order is the internal
-    heap order, which already differs between its debug and release builds); the set of rows per
-    agent is identical. knn_index_tensor() gives the road-entity index of every row.
+  * agent_roadmap rows: with AllEntitiesWithRadiusFiltering (the env default, "linear") they come in
+    road-entity index order exactly like the reference's (src/sim.cpp:261-279). With
+    KNearestEntitiesWithRadiusFiltering the reference leaves them in its internal heap order, which
+    already differs between its debug and release builds; here they come by distance band, then by
+    position in the spatially sorted road table. The set of rows per agent is identical;
+    knn_index_tensor() gives the road-entity index of every row.
+  * Streams: the engine launches on a blocking CUDA stream, so tensor writes made with torch on its
+    default stream are ordered before step() / reset() without an explicit synchronize, as with the
+    reference.
 """
 from __future__ import annotations
 
@@ -210,6 +216,17 @@ class SimManager:
         a = (C.c_int32 * max(n, 1))(*[int(w) for w in worlds])
         b = (C.c_int32 * max(n, 1))(*[int(s) for s in scene_ids])
         _capi.check(self._lib.gd_bind_worlds(self._h, a, b, n))
+
+    def auto_reset_pool(self, scene_ids):
+        """Register the pooled scene ids (pool_add) the device-side auto-reset cycles through."""
+        n = len(scene_ids)
+        a = (C.c_int32 * max(n, 1))(*[int(s) for s in scene_ids])
+        _capi.check(self._lib.gd_auto_reset_pool(self._h, a, n))
+
+    def auto_reset(self):
+        """After a step: every world whose controlled agents are all done moves on to its next pooled scenario,
+        is reset and has its observations recomputed - on the device, stream-ordered, no host round trip."""
+        _capi.check(self._lib.gd_auto_reset(self._h))
 
     def stats(self) -> dict:
         s = _capi.GdStats()

@@ -10,6 +10,14 @@
  * Threading: one caller thread per handle. gd_step / gd_reset / gd_set_maps / gd_delete_agents
  * return after the device is idle, as Manager::step does (external/madrona/src/mw/cuda_exec.cpp:1892).
  * Tensor pointers are device pointers on GdConfig.gpu_id and stay valid for the handle's lifetime.
+ *
+ * Stream contract: the engine launches on its own *blocking* stream (gd_stream()), as Madrona does
+ * (external/madrona/include/madrona/cuda_utils.inl:62). Writes into the action tensor (or any other tensor) that
+ * the caller enqueued on the legacy default stream - what torch does by default, e.g.
+ * `sim.action_tensor().to_torch()[:, :, :3].copy_(a)` (gpudrive/env/env_torch.py:652) - are therefore ordered
+ * before the next gd_step / gd_step_async / gd_reset / gd_policy_obs ..., and the caller's later reads on that
+ * stream after them; no explicit synchronisation is needed. A caller that writes from a non-blocking stream of
+ * its own must order that stream against gd_stream() itself.
  */
 #ifndef GPUDRIVE_B200_H
 #define GPUDRIVE_B200_H
@@ -99,8 +107,11 @@ typedef struct GdStats {
     uint64_t steps;
     uint64_t agent_steps;        /* live agents x steps */
     uint64_t controlled_steps;   /* live controlled agents x steps */
-    uint64_t episodes_reset;
+    uint64_t episodes_reset;     /* worlds reset by any route (ctor, reset, set_maps, bind_worlds, auto_reset) */
+    /* (agent, step) pairs at which Info.collidedWith{Road,Vehicle,NonVehicle} / Info.reachedGoal / Done went
+     * 0 -> 1 (src/sim.cpp:597-626,713-724), accumulated on the device by the step kernel */
     uint64_t collided_road, collided_vehicle, collided_nonvehicle, goals_reached, dones;
+    uint64_t sat_tests;          /* two-sided OBB SAT tests evaluated (pairs that survived the cheap rejects) */
 } GdStats;
 
 /* Manager::Manager(cfg) — src/mgr.cpp:565 (Impl::init :399-563, then reset({})). num_worlds = n_scenes. */
@@ -151,6 +162,14 @@ int gd_expert_actions(GdHandle h, GdTensorDesc *out);
 /* Device scenario pool: load a scenario once, re-bind worlds to pooled scenarios + reset them. */
 int gd_pool_add(GdHandle h, const char *scene_path, int32_t *scene_id_out);
 int gd_bind_worlds(GdHandle h, const int32_t *worlds, const int32_t *scene_ids, int32_t n);
+/* Device-side auto-reset from the scenario pool (BASELINE config 4; replaces the env's host loop "find finished
+ * worlds -> sim.reset(list)" of gpudrive/env/env_puffer.py and the set_maps resampling of
+ * gpudrive/env/env_torch.py:1351-1370). gd_auto_reset_pool registers the pooled scene ids once (world w starts at
+ * entry w % n). gd_auto_reset, called after a step, finds on the device every world whose controlled agents are
+ * all done, advances its cursor (cursor + 1 + w % (n - 1)) % n, re-binds it to that pooled scene, resets it and
+ * recomputes its observations - stream-ordered, without a host round trip, and without waiting for the device. */
+int gd_auto_reset_pool(GdHandle h, const int32_t *scene_ids, int32_t n);
+int gd_auto_reset(GdHandle h);
 /* Scenario pool files (replaces the per-world MapReader JSON parse of Manager::Impl::init /
  * setMaps, src/mgr.cpp:399-470,590-654, for pools that are loaded again and again). gd_pool_convert parses
  * n JSON scenarios on `threads` host threads (<= 0: all cores) and writes them into one binary file; the file
@@ -161,8 +180,11 @@ int gd_pool_convert(const char *const *json_paths, int32_t n, float polylineRedu
 int gd_pool_count(const char *pool_path, int32_t *count_out, float *threshold_out);
 int gd_stats(GdHandle h, GdStats *out);
 /* Engine options (no reference equivalent): GD_OPT_KNN_INDEX (default 1) writes the GD_T_KNN_INDEX side
- * buffer; GD_OPT_PROFILE (default 0) brackets the two step kernels with CUDA events on the engine stream. */
-enum GdOption { GD_OPT_KNN_INDEX = 0, GD_OPT_PROFILE = 1 };
+ * buffer; GD_OPT_PROFILE (default 0) brackets the two step kernels with CUDA events on the engine stream;
+ * GD_OPT_GRAPH (default 1) launches a step as one CUDA graph (the reference's GPU backend does,
+ * external/madrona/src/mw/cuda_exec.cpp:1699,1891); GD_OPT_ASYNC_AUX (default 0) lets gd_policy_obs /
+ * gd_shaped_reward / gd_expert_actions return without waiting for the device. */
+enum GdOption { GD_OPT_KNN_INDEX = 0, GD_OPT_PROFILE = 1, GD_OPT_GRAPH = 2, GD_OPT_ASYNC_AUX = 3 };
 int gd_set_option(GdHandle h, int32_t option, int32_t value);
 /* Accumulated device time (ms) of k_agents / k_obs over the steps taken since GD_OPT_PROFILE was enabled. */
 int gd_kernel_times(GdHandle h, double *agents_ms, double *obs_ms, int64_t *steps);

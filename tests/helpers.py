@@ -18,6 +18,7 @@ REF_EXAMPLES = "/root/reference/data/processed/examples"
 # max(|reference|, scale) where scale is the natural magnitude of the quantity (positions live in
 # a +-150 m world, so scale = 100 m; angles and unit quantities use 1).
 RTOL = 1e-5
+TIE_RTOL = 1e-5        # a kNN / radius boundary difference is forgiven only inside the float tolerance
 POS_SCALE = 100.0
 
 
@@ -36,39 +37,7 @@ def ref_params(d):
     return RefParams(**d)
 
 
-def engine_params(d):
-    from gpudrive_lab_b200 import madrona_gpudrive as mg
-    p = mg.Parameters()
-    for k, v in d.items():
-        if k == "rewardType":
-            p.rewardParams.rewardType = v
-        elif k in ("distanceToGoalThreshold", "distanceToExpertThreshold"):
-            setattr(p.rewardParams, k, v)
-        else:
-            setattr(p, k, v)
-    return p
-
-
-def random_actions(step, W, S, model, seed=42):
-    """Seeded per (seed, step) action block [W,S,10] (mirrors tests/bicyclemodel.cpp:73-75 ranges)."""
-    rng = np.random.Generator(np.random.PCG64([seed, step]))
-    a = np.zeros((W, S, 10), np.float32)
-    if model in (0, 1):      # Classic / InvertibleBicycle: acceleration, steering, head angle
-        a[..., 0] = rng.uniform(-3.0, 2.0, (W, S))
-        a[..., 1] = rng.uniform(-0.7, 0.7, (W, S))
-        a[..., 2] = rng.uniform(-0.3, 0.3, (W, S))
-    elif model == 2:         # DeltaLocal: dx, dy, dyaw
-        a[..., 0] = rng.uniform(-0.5, 1.5, (W, S))
-        a[..., 1] = rng.uniform(-0.2, 0.2, (W, S))
-        a[..., 2] = rng.uniform(-0.05, 0.05, (W, S))
-    else:                    # State: position(3), yaw, velocity(6)
-        a[..., 0] = rng.uniform(-100, 100, (W, S))
-        a[..., 1] = rng.uniform(-100, 100, (W, S))
-        a[..., 2] = 1.0
-        a[..., 3] = rng.uniform(-3, 3, (W, S))
-        a[..., 4] = rng.uniform(-10, 10, (W, S))
-        a[..., 5] = rng.uniform(-10, 10, (W, S))
-    return a
+from gpudrive_lab_b200.workload import engine_params, random_actions  # noqa: E402,F401  (shared with bench.py)
 
 
 def close(a, b, scale=1.0, rtol=RTOL):
@@ -79,6 +48,27 @@ def close(a, b, scale=1.0, rtol=RTOL):
 
 class Mismatch(AssertionError):
     pass
+
+
+# One line per parity run, printed by conftest.pytest_terminal_summary so the exemption counters are visible in
+# the tail of a `pytest -q` log (north_star: index sets bit-exact, floats 1e-5; every exemption is counted).
+PARITY_REPORT: list[str] = []
+EXEMPTIONS = ("knn_boundary_ties", "partner_radius_ties", "lidar_mismatch")
+
+
+def report(tag, stats, allowed=None):
+    """Record a parity run's counters and fail on any exemption that was not individually allowed.
+    allowed: dict counter -> (max count, reason)."""
+    allowed = allowed or {}
+    line = f"parity[{tag}] " + " ".join(f"{k}={stats.get(k, 0)}" for k in
+                                        ("knn_agents", "lidar_rays") + EXEMPTIONS)
+    for k, (n, why) in allowed.items():
+        line += f" (allowed {k}<={n}: {why})"
+    PARITY_REPORT.append(line)
+    print(line)
+    for k in EXEMPTIONS:
+        lim = allowed.get(k, (0, ""))[0]
+        assert stats.get(k, 0) <= lim, f"{tag}: {k} = {stats.get(k, 0)} > {lim} (unexplained exemption)"
 
 
 def compare_step(ref, eng, radius, lidar, tag="", stats=None):
@@ -131,7 +121,7 @@ def compare_step(ref, eng, radius, lidar, tag="", stats=None):
                 for (i, j) in bad:
                     row = pr[i, j] if pr[i, j, 8] >= 0 else pe[i, j]
                     dist = float(np.hypot(row[1], row[2]))
-                    if abs(dist - radius) > 1e-3 * radius:
+                    if abs(dist - radius) > TIE_RTOL * radius:
                         fail(f"w{w} agent{i} partner row {j} id differs ref={pr[i, j]} eng={pe[i, j]}")
                     stats["partner_radius_ties"] = stats.get("partner_radius_ties", 0) + 1
             m = same_id
@@ -194,7 +184,7 @@ def _match_rows(r_rows, e_rows):
         hit = -1
         for j in js:
             dh = abs(((e_rows[i, 5] - r_rows[j, 5]) + np.pi) % (2 * np.pi) - np.pi)
-            if dh <= 1e-4 and np.array_equal(e_rows[i, 6:9], r_rows[j, 6:9]) and \
+            if dh <= RTOL * np.pi and np.array_equal(e_rows[i, 6:9], r_rows[j, 6:9]) and \
                     np.allclose(e_rows[i, 2:5], r_rows[j, 2:5], rtol=1e-6, atol=0):
                 hit = j
                 break
@@ -207,7 +197,8 @@ def _match_rows(r_rows, e_rows):
 
 def _boundary_tie(r_rows, e_rows, radius, unmatched):
     """True if every difference between the two sets sits on the selection boundary: squared
-    distance within 1e-5 relative of the largest selected one, or distance within 1e-5 of the radius."""
+    distance within 1e-5 relative of the largest selected one, or distance within 1e-5 of the radius
+    (north_star's float tolerance: the two sides round the key of such a pair differently)."""
     if abs(len(r_rows) - len(e_rows)) > 1 or len(unmatched) > 1:
         return False
     def edge(rows, idxs):
@@ -216,7 +207,7 @@ def _boundary_tie(r_rows, e_rows, radius, unmatched):
             return True
         lim = d2.max()
         for i in idxs:
-            if not (abs(d2[i] - lim) <= 1e-4 * lim or abs(np.sqrt(d2[i]) - radius) <= 1e-4 * radius):
+            if not (abs(d2[i] - lim) <= TIE_RTOL * lim or abs(np.sqrt(d2[i]) - radius) <= TIE_RTOL * radius):
                 return False
         return True
     if not edge(e_rows, unmatched):
@@ -225,7 +216,7 @@ def _boundary_tie(r_rows, e_rows, radius, unmatched):
         # the extra row of the longer side must be at the radius
         longer = r_rows if len(r_rows) > len(e_rows) else e_rows
         d = np.sqrt(longer[:, 0].astype(np.float64) ** 2 + longer[:, 1] ** 2)
-        return bool((np.abs(d - radius) <= 1e-4 * radius).any())
+        return bool((np.abs(d - radius) <= TIE_RTOL * radius).any())
     return True
 
 

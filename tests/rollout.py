@@ -4,11 +4,11 @@ from __future__ import annotations
 
 import numpy as np
 
-from helpers import (compare_step, engine_params, random_actions, ref_params, snapshot_engine,
+from helpers import (compare_step, engine_params, random_actions, ref_params, report, snapshot_engine,
                      snapshot_ref)
 
 
-def run_parity(scenes, pd, steps, S=128, seed=42, check_every=1, names=None):
+def run_parity(scenes, pd, steps, S=128, seed=42, check_every=1, names=None, tag=None, allowed=None):
     import torch
     from gpudrive_lab_b200 import madrona_gpudrive as mg
     from oracle.refmgr import RefManager
@@ -37,4 +37,8 @@ def run_parity(scenes, pd, steps, S=128, seed=42, check_every=1, names=None):
         # the reference clips actions in place (dynamics.hpp:55-56); so must we
         if model == 1:
             assert np.array_equal(act_r[..., :2], act_e.cpu().numpy()[..., :2]), "clipped action write-back differs"
+    if tag is None:
+        import inspect
+        tag = inspect.stack()[1].function
+    report(tag, stats, allowed)
     return ref, sim, stats

@@ -30,8 +30,7 @@ def test_bicycle_ignore_full_episode(synth_dir):
     _need()
     scenes = _scenes(synth_dir, 2)
     pd = param_dict(dynamicsModel=1, collisionBehaviour=2)
-    _, _, stats = run_parity(scenes, pd, 91)
-    assert stats.get("knn_boundary_ties", 0) <= 1e-3 * stats["knn_agents"]
+    run_parity(scenes, pd, 91)          # (helpers.report: every exemption counter must be 0)
 
 
 def test_delta_lidar_full_episode(synth_dir):
@@ -39,8 +38,7 @@ def test_delta_lidar_full_episode(synth_dir):
     _need()
     scenes = _scenes(synth_dir, 2)
     pd = param_dict(dynamicsModel=2, enableLidar=True)
-    _, _, stats = run_parity(scenes, pd, 91)
-    assert stats["lidar_mismatch"] <= 1e-4 * stats["lidar_rays"]
+    run_parity(scenes, pd, 91)
 
 
 def test_agent_stop_collisions(synth_dir):
@@ -62,12 +60,27 @@ def test_agent_removed_classic(synth_dir):
 
 def test_expert_replay_linear_roadmap(synth_dir):
     """No controlled agents (pure expert replay, tests/test_expert.py) + the env-default 'linear'
-    road algorithm (AllEntitiesWithRadiusFiltering)."""
+    road algorithm (AllEntitiesWithRadiusFiltering), whose row ORDER is part of the contract: the first K
+    in-radius entities in road-index order (src/sim.cpp:261-279)."""
     _need()
+    from helpers import close, POS_SCALE
     scenes = _scenes(synth_dir, 2)
     pd = param_dict(dynamicsModel=1, maxNumControlledAgents=0, roadObservationAlgorithm=1,
                     collisionBehaviour=0, isStaticAgentControlled=False)
-    run_parity(scenes, pd, 91)
+    ref, sim, _ = run_parity(scenes, pd, 91)
+    rr = ref.tensor("agent_roadmap")
+    re_ = sim.agent_roadmap_tensor().to_torch().cpu().numpy()
+    shape = ref.tensor("shape")
+    rows = 0
+    for w in range(2):
+        A = int(shape[w, 0])
+        r, e = rr[w, :A], re_[w, :A]
+        # row for row: type / id / mapType and the scale exact, ego-frame position and heading 1e-5
+        assert np.array_equal(r[..., 6:9], e[..., 6:9]), "linear road-map rows are not in the reference's order"
+        assert np.array_equal(r[..., 2:5], e[..., 2:5])
+        assert close(e[..., 0:2], r[..., 0:2], POS_SCALE).all()
+        rows += int((r[..., 6] != 0).sum())
+    assert rows > 1000
 
 
 def test_state_model_and_distance_reward(synth_dir):
