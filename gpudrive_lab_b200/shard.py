@@ -8,7 +8,7 @@ from __future__ import annotations
 from typing import Sequence
 
 STAT_FIELDS = ("steps", "agent_steps", "controlled_steps", "episodes_reset", "collided_road",
-               "collided_vehicle", "collided_nonvehicle", "goals_reached", "dones")
+               "collided_vehicle", "collided_nonvehicle", "goals_reached", "dones", "sat_tests")
 
 
 def world_block(total_worlds: int, rank: int, world_size: int) -> range:

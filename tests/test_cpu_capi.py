@@ -30,7 +30,7 @@ def test_struct_layouts_match_header():
     assert C.sizeof(_capi.GdParams) == 15 * 4
     assert C.sizeof(_capi.GdConfig) == 8 + 15 * 4 + 4
     assert C.sizeof(_capi.GdTensorDesc) == 8 + 4 + 4 + 8 * 8 + 8      # device + padding
-    assert C.sizeof(_capi.GdStats) == 9 * 8
+    assert C.sizeof(_capi.GdStats) == 10 * 8
     assert len(_capi.TENSOR_IDS) == 23
 
 
