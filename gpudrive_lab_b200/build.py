@@ -12,7 +12,7 @@ OUT = os.path.join(HERE, "libgpudrive_b200.so")
 SOURCES = ["engine.cu", "scenario.cpp", "capi.cpp"]
 HEADERS = ["engine.h", "gd_types.h", "scenario.h", "json_min.h", "glibc_trig.h", "device_math.cuh", "kernels_step.cuh",
            "kernels_obs.cuh", "kernels_obs_main.cuh", "kernels_reset.cuh", "kernels_bev.cuh", "kernels_policy.cuh",
-           "kernels_env.cuh", os.path.join("..", "..", "include", "gpudrive_b200.h")]
+           "kernels_env.cuh", "kernels_lidar_fix.cuh", os.path.join("..", "..", "include", "gpudrive_b200.h")]
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",

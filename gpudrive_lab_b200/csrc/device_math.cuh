@@ -23,6 +23,15 @@ __device__ __forceinline__ float cos_hp(float x) {
 __device__ __forceinline__ float sin_hp(float x) {
     return gdtrig::in_fast_range(x) ? gdtrig::sinf_glibc(x) : (float)sin((double)x);
 }
+// sin and cos of one angle with glibc's results: the one-pass restatement where it is valid, fp64 beyond
+// (|x| >= 120: only a caller-supplied head angle can get there; kept out of line, it is never on a hot path)
+__device__ __noinline__ void sincos_far(float x, float *s, float *c) {
+    *s = (float)sin((double)x); *c = (float)cos((double)x);
+}
+__device__ __forceinline__ void sincos_hp(float x, float &s, float &c) {
+    if (gdtrig::in_fast_range(x)) gdtrig::sincosf_glibc(x, s, c);
+    else sincos_far(x, &s, &c);
+}
 __device__ __forceinline__ float tan_hp(float x) { return (float)tan((double)x); }
 __device__ __forceinline__ float atan_hp(float x) { return (float)atan((double)x); }
 __device__ __forceinline__ float atan2_hp(float y, float x) { return (float)atan2((double)y, (double)x); }

@@ -9,6 +9,7 @@
 
 #include "kernels_bev.cuh"
 #include "kernels_env.cuh"
+#include "kernels_lidar_fix.cuh"
 #include "kernels_obs_main.cuh"
 #include "kernels_policy.cuh"
 #include "kernels_reset.cuh"
@@ -139,6 +140,7 @@ void Engine::allocExports() {
     st_.world_scene = devAlloc<int32_t>(owned_, W_);
     st_.reset_flag = devAlloc<int32_t>(owned_, W_);
     st_.stats = devAlloc<unsigned long long>(owned_, 16);
+    st_.retrace = devAlloc<uint32_t>(owned_, 1 + (size_t)kRetraceCap);
     d_worklist_ = devAlloc<int32_t>(owned_, 2 * (size_t)W_);
     d_act_stage_ = devAlloc<float>(owned_, (size_t)W_ * S_ * kActionSize);
 }
@@ -518,6 +520,10 @@ void Engine::buildStepGraph(const StepGraphKey &key) {
         void *args[] = {&scenes, &st_, &ex_, &params_, &S, &groups, &knn, &key_thr, &zero};
         add_kernel((void *)k_obs, dim3(W_ * groups), dim3(OBS_BLOCK), sizeof(ObsSmem), args);
     }
+    if (params_.enableLidar) {      // the few rays k_obs could not settle, re-traced exactly (counted with k_obs' time)
+        void *args[] = {&scenes, &st_, &ex_, &S};
+        add_kernel((void *)k_lidar_fix, dim3(FIX_GRID), dim3(FIX_BLOCK), 0, args);
+    }
     if (key.profile) add_event(prof_ev_[2], &graph_ev_nodes_[2]);
     if (bev_enabled_) {
         void *args[] = {&scenes, &st_, &ex_, &params_, &S, &key_thr};
@@ -534,7 +540,7 @@ void Engine::launchRest(bool decrement, bool only_flagged) {
     const size_t smem_agents = sizeof(AgentBox) * (size_t)S_;
     const bool prof = opt_profile_ && decrement;
     const int groups = obsGroups();
-    kernels_per_step_ = bev_enabled_ ? 3 : 2;
+    kernels_per_step_ = 2 + (bev_enabled_ ? 1 : 0) + (params_.enableLidar ? 1 : 0);
     cudaEvent_t *ev = nullptr;
     if (prof) {
         if (prof_pending_ == kProfRing) foldProfile();
@@ -560,6 +566,7 @@ void Engine::launchRest(bool decrement, bool only_flagged) {
     if (mark_agents_done_) GD_CUDA(cudaEventRecord(ev_agents_, stream_));   // reward / done / info are final here
     k_obs<<<W_ * groups, OBS_BLOCK, sizeof(ObsSmem), stream_>>>(d_scenes_, st_, ex_, params_, S_, groups,
                                                                 opt_knn_idx_, key_thr_, flagged);
+    if (params_.enableLidar) k_lidar_fix<<<FIX_GRID, FIX_BLOCK, 0, stream_>>>(d_scenes_, st_, ex_, S_);
     if (prof) { GD_CUDA(cudaEventRecord(ev[2], stream_)); prof_pending_++; }
     if (bev_enabled_)
         k_bev<<<W_ * S_, BEV_BLOCK, sizeof(BevSmem), stream_>>>(d_scenes_, st_, ex_, params_, S_, key_thr_);
@@ -740,7 +747,8 @@ TensorDesc Engine::policyObs(int normalize) {
     GD_CUDA(cudaSetDevice(gpu_));
     const int width = kPolicyEgo + (S_ - 1) * kPolicyPartner + kMaxAgentMapObs * kPolicyRoad;
     if (!d_policy_obs_) d_policy_obs_ = devAlloc<float>(owned_, (size_t)W_ * S_ * width);
-    k_policy_obs<<<W_ * S_, 256, 0, stream_>>>(ex_, d_policy_obs_, S_, normalize ? 1 : 0);
+    if (normalize == 2) k_policy_obs<true><<<W_ * S_, 256, 0, stream_>>>(ex_, d_policy_obs_, S_, 1);
+    else k_policy_obs<false><<<W_ * S_, 256, 0, stream_>>>(ex_, d_policy_obs_, S_, normalize ? 1 : 0);
     launches_++;
     GD_CUDA(cudaGetLastError());
     if (!opt_async_aux_) GD_CUDA(cudaStreamSynchronize(stream_));

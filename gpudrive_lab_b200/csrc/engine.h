@@ -16,6 +16,7 @@
 namespace gd {
 
 constexpr int kMaxZClasses = 8;
+constexpr unsigned kRetraceCap = 1u << 16;
 
 // Device view of one pooled scenario (all pointers into the pool arena).
 struct SceneDev {
@@ -83,6 +84,7 @@ struct StateDev {
     int32_t *collided;    // [W,S] CollisionDetectionEvent.hasCollided
     int32_t *world_scene; // [W]
     int32_t *reset_flag;  // [W]
+    uint32_t *retrace;         // [1 + kRetraceCap] lidar rays k_obs hands to k_lidar_fix: count, then slot * 150 + ray
     unsigned long long *stats; // [16] episode statistics accumulators (StatSlot), written by k_agents
 };
 

@@ -126,4 +126,23 @@ GDT_FN float cosf_glibc(float y) {
     return (float)poly_cos(r2, p);
 }
 
+// sinf and cosf of the same argument in one pass: one range reduction and both polynomials, straight-line
+// (selects instead of the library's branches). For |y| < pi/4 the library's short path is the general one with
+// n = 0 (r = x exactly, first table, sign +1), so only the |y| < 2^-12 returns need a select. Bit-identical to
+// sinf_glibc / cosf_glibc above (tests/csrc/check_trig.cpp sweeps all three against libm).
+GDT_FN void sincosf_glibc(float y, float &s_out, float &c_out) {
+    const double x = (double)y;
+    const uint32_t top = abstop12(y);
+    int n;
+    const double r = reduce_fast(x, n);
+    const Tab p = tab((n & 2) != 0);
+    const double r2 = GDT_MUL(r, r);
+    const double sign = ((n & 3) == 1 || (n & 3) == 2) ? -1.0 : 1.0;
+    const float ps = (float)poly_sin(GDT_MUL(r, sign), r2, p);
+    const float pc = (float)poly_cos(r2, p);
+    const bool odd = (n & 1) != 0, tiny = top <= 0x397;
+    s_out = tiny ? y : (odd ? pc : ps);
+    c_out = tiny ? 1.0f : (odd ? ps : pc);
+}
+
 } // namespace gdtrig

@@ -62,7 +62,7 @@ struct ObsWarpSmem {
     union {
         struct {
             uint32_t bt[3 * NRAY];            // lidar: bits of the closest hit distance per plane and ray (none: ~0)
-            uint16_t bid[3 * NRAY];           // and its box: sorted road slot, or 0x4000 | agent slot
+            uint16_t bid[3 * NRAY];           // and its box: sorted road slot, or 0x4000 | agent slot; 0x8000: marginal hit
         } l;
         float stage[32 * 9 + 4];              // row transpose buffer for coalesced stores (+ up to 3 floats of misalignment)
     } u;
@@ -74,6 +74,7 @@ struct ObsWarpSmem {
         } g;
         uint32_t hist[256];                   // radix-select histogram
     } v;
+    uint8_t own[32];                          // clip stage: the r-th lane that brought a non-empty ray range
 };
 
 struct ObsSmem {
@@ -113,21 +114,33 @@ __device__ __forceinline__ float rcp_fast(float x) {
 
 // Clip one ray against one box in the box frame (pure rotation, unscaled): equivalent to
 // traceRayIntoConvexPolyhedron over the four vertical faces (broadphase.cpp:754-855) with
-// tfirst = 0, tlast = lidarDistance, "entering t >= tfirst" and "only back faces -> miss".
+// tfirst = 0, tlast = lidarDistance, "entering t >= tfirst" and "only back faces -> miss" - up to rounding.
+// The reference decides hit / miss in its own float arithmetic (object space, IEEE divisions); this fast form
+// (approximate reciprocals, fused multiply-adds) can disagree with it when the ray grazes a corner, starts on a
+// face or ends at the range limit. So the test is widened by `slack`, a bound on that disagreement - the slab
+// parameters carry a few ulp of the box-frame coordinates, scaled by |1 / direction component|^2 - and every hit
+// or near-miss inside the slack is flagged `marginal`: if such a hit wins its ray, the write-out settles it with
+// the reference's exact clip (and, should that say miss, hands the ray to k_lidar_fix for an exact re-trace).
+// Nothing exported ever rests on this function's rounding.
 // (px, py): ray origin in the box frame. Explicit fmaf: this translation unit is compiled with --fmad=false.
 __device__ __forceinline__ float ray_box(float px, float py, float cphi, float sphi, float d0, float d1,
-                                         float dx, float dy)
+                                         float dx, float dy, bool &marginal)
 {
-    // Branch-free slabs. A direction component of exactly 0 gives an infinite reciprocal: both slab
-    // parameters become -inf / +inf (origin between the planes: no constraint) or the same infinity (origin
-    // outside: tnear > tfar, a miss); fminf / fmaxf drop the NaN of 0 * inf (origin exactly on a plane).
+    // Branch-free slabs. A direction component of exactly 0 gives an infinite reciprocal (and an infinite slack:
+    // the pair is settled exactly); fminf / fmaxf drop the NaN of 0 * inf (origin exactly on a plane).
     const float lx = fmaf(cphi, dx, sphi * dy), ly = fmaf(cphi, dy, -(sphi * dx));   // direction in box frame
     const float ivx = rcp_fast(lx), ivy = rcp_fast(ly);
     const float x1 = (-d0 - px) * ivx, x2 = (d0 - px) * ivx;
     const float y1 = (-d1 - py) * ivy, y2 = (d1 - py) * ivy;
     const float tnear = fmaxf(fminf(x1, x2), fminf(y1, y2));
     const float tfar = fminf(kLidarDistance, fminf(fmaxf(x1, x2), fmaxf(y1, y2)));
-    return (tnear >= 0.f && tnear <= tfar) ? tnear : -1.f;
+    // |error of a slab parameter| <~ 5 eps * (box-frame coordinates) * (1 / direction component)^2: the direction
+    // component carries ~3 eps of absolute error (the box axis from its quaternion, one fma), i.e. 3 eps /
+    // |component| relative, which multiplies the parameter; the approximate reciprocal adds 1-2 ulp
+    const float iv = fabsf(ivx) + fabsf(ivy);
+    const float slack = 6e-7f * ((fabsf(px) + fabsf(py)) + (d0 + d1)) * iv * iv;
+    marginal = !(tnear >= slack) || !(tnear + slack <= tfar);
+    return (tnear >= -slack && tnear <= tfar + slack) ? fmaxf(tnear, 0.f) : -1.f;
 }
 
 // The same clip with the reference's own arithmetic: ray moved into object space (rotate, divide by the
@@ -278,8 +291,8 @@ __device__ __forceinline__ int plane_mask(float pz, float bz, float d2, float zm
 
 // ------------------------------------------------------------------------------------------
 // lidar clip stage: every lane brings one box and a ray range [lo, lo + n); the warp expands the 32
-// ranges into (box, ray) pairs, 32 pairs per round, one pair per lane. A lane finds its pair by a
-// binary search over the inclusive prefix sums and fetches the box from its owner with shuffles, so
+// ranges into (box, ray) pairs, 32 pairs per round, one pair per lane. A lane finds its pair's owner in a
+// small per-warp table (see lidar_expand) and fetches the box from that lane with shuffles, so
 // no queue and no reload of the box are needed. The closest hit per (plane, ray) is kept as a native
 // 32-bit shared atomicMin on the bits of t; the box id is written by whichever lane holds the minimum
 // after the round's atomics (warp-synchronous, so the last writer is always the current minimum).
@@ -302,11 +315,16 @@ __device__ __forceinline__ void lidar_commit(ObsWarpSmem &wp, bool hit, int ray,
     }
 }
 
+// The owner of pair j - the lane whose ray range contains it - without a search: the lanes that brought a range are
+// listed once (wp.own); per round one warp OR collects the positions at which a new owner's range starts, and a
+// lane's owner is the last one that started at or before its position: a popc and a byte load, where a binary
+// search over the prefix sums took five dependent shuffles.
 __device__ __forceinline__ void lidar_expand(ObsWarpSmem &wp, int lane, int lo, int n, int pm, unsigned id,
                                              float relx, float rely, float cphi, float sphi, float d0, float d1)
 {
     const unsigned FULL = 0xffffffffu;
-    if (!__any_sync(FULL, n > 0)) return;
+    const unsigned live = __ballot_sync(FULL, n > 0);
+    if (!live) return;
     // ray origin in the box frame (the box centre is (relx, rely) away from the origin)
     const float opx = -fmaf(cphi, relx, sphi * rely), opy = -fmaf(cphi, rely, -(sphi * relx));
     int incl = n;
@@ -318,24 +336,38 @@ __device__ __forceinline__ void lidar_expand(ObsWarpSmem &wp, int lane, int lo, 
     const int total = __shfl_sync(FULL, incl, 31);
     GD_CNT(5, total); GD_CNT(6, 1);
     const int excl = incl - n;
+    if (n > 0) wp.own[__popc(live & ((1u << lane) - 1u))] = (uint8_t)lane;
+    __syncwarp();
     const unsigned meta = (unsigned)(lo - excl + 2048) | ((unsigned)pm << 12) | (id << 15);   // lo - excl in [-1600, 49]
+    int r0 = 0;                                       // owners whose range starts before this round
+#pragma unroll 1
     for (int base = 0; base < total; base += 32) {
         const int j = base + lane;
-        int s = 0;                                   // owner: first lane whose inclusive sum exceeds j
+        const unsigned rel = (unsigned)(excl - base);
+        const unsigned starts = __reduce_or_sync(FULL, (n > 0 && rel < 32u) ? (1u << rel) : 0u);
+#ifdef GD_OBS_BSEARCH      // kernel experiments: the round-1 owner search, five dependent shuffles
+        int s = 0;
 #pragma unroll
         for (int step = 16; step > 0; step >>= 1) {
             const int v = __shfl_sync(FULL, incl, s + step - 1);
             if (v <= j) s += step;
         }
+        (void)starts;
+#else
+        const int s = wp.own[r0 + __popc(starts & (FULL >> (31 - lane))) - 1];      // (round 0 starts at position 0)
+        r0 += __popc(starts);
+#endif
         const float spx = __shfl_sync(FULL, opx, s), spy = __shfl_sync(FULL, opy, s);
         const float sc_ = __shfl_sync(FULL, cphi, s), ss_ = __shfl_sync(FULL, sphi, s);
         const float sd0 = __shfl_sync(FULL, d0, s), sd1 = __shfl_sync(FULL, d1, s);
         const unsigned smeta = __shfl_sync(FULL, meta, s);
         const int ray = min(max((int)(smeta & 4095u) - 2048 + j, 0), NRAY - 1);   // (clamped for the lanes past `total`)
         const float2 d = wp.v.g.raydir[ray];
-        const float t = ray_box(spx, spy, sc_, ss_, sd0, sd1, d.x, d.y);
+        bool marginal;
+        const float t = ray_box(spx, spy, sc_, ss_, sd0, sd1, d.x, d.y, marginal);
         GD_CNT(9, 1);
-        lidar_commit(wp, j < total && t >= 0.f, ray, __float_as_uint(t), smeta >> 15, (int)((smeta >> 12) & 7u));
+        lidar_commit(wp, j < total && t >= 0.f, ray, __float_as_uint(t), ((smeta >> 15) & 0x7fffu) | (marginal ? 0x8000u : 0u),
+                     (int)((smeta >> 12) & 7u));
     }
     __syncwarp();
 }

@@ -131,10 +131,15 @@ k_obs(const SceneDev *__restrict__ scenes, StateDev st, Exports ex, Params prm, 
             // (ray 0: 0 / NRAY = 0 without the slow path IEEE division takes for a zero operand)
             const float frac = i == 0 ? 0.f : __fdiv_rn(i == 0 ? 1.f : 2.f * (float)i, (float)NRAY);
             const float theta = __fadd_rn(__fmul_rn(kLidarAngle, __fsub_rn(frac, 1.f)), head);
-            // sim.cpp:411-412. Observation output with a 1e-5 bar, not agent state: CUDA's sincosf (<= 2 ulp
-            // from glibc's cosf / sinf) instead of the bit-exact restatement, which costs four times as much.
+            // sim.cpp:411-412, with glibc's own cosf / sinf (one-pass restatement, bit-identical). A direction that
+            // is 1 ulp off moves the depth of a ray that runs nearly parallel to a long thin box by far more than
+            // 1e-5 (CUDA's sincosf, <= 2 ulp away, cost 7 of 2.4 M rays their parity on the benchmarked scenes).
             float x, y;
+#ifdef GD_OBS_FAST_DIRS
             sincosf(theta, &y, &x);
+#else
+            sincos_hp(theta, y, x);
+#endif
             const float dx = __fadd_rn(__fmul_rn(x, rgx), __fmul_rn(y, fwx));
             const float dy = __fadd_rn(__fmul_rn(x, rgy), __fmul_rn(y, fwy));
             const float inv = __fdiv_rn(1.f, __fsqrt_rn(__fadd_rn(len2_xy(dx, dy), 0.f)));
@@ -152,6 +157,7 @@ k_obs(const SceneDev *__restrict__ scenes, StateDev st, Exports ex, Params prm, 
         }
         __syncwarp();
         // other agents first: few boxes, and their hits close rays before the road groups are visited
+#pragma unroll 1
         for (int base = 0; base < A; base += 32) {
             const int j = base + lane;
             int pm = 0, lo = 0, n = 0;
@@ -308,8 +314,9 @@ k_obs(const SceneDev *__restrict__ scenes, StateDev st, Exports ex, Params prm, 
         for (int i = lane; i < 3 * NRAY; i += 32) {
             const uint32_t tbits = wp.u.l.bt[i];
             float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+            bool retrace = false;
             if (tbits != 0xffffffffu) {
-                float t = __uint_as_float(tbits);
+                float t;
                 const unsigned id = wp.u.l.bid[i];
                 float bx, by, bqw, bqz, d0, d1; int type;
                 if (id & 0x4000u) {
@@ -317,21 +324,31 @@ k_obs(const SceneDev *__restrict__ scenes, StateDev st, Exports ex, Params prm, 
                     const float4 o0 = sm.a0[j]; const float4 gb = sc.ag_b[j];
                     bx = o0.x; by = o0.y; bqw = o0.z; bqz = o0.w; d0 = gb.x; d1 = gb.y; type = (int)gb.w;
                 } else {
-                    const float4 ra = __ldg(&sc.s_a[id]); const float2 rb = __ldg(&sc.s_b[id]);
+                    const int e = id & 0x3fff;
+                    const float4 ra = __ldg(&sc.s_a[e]); const float2 rb = __ldg(&sc.s_b[e]);
                     bx = ra.x; by = ra.y; bqw = ra.z; bqz = ra.w; d0 = rb.x; d1 = rb.y;
-                    type = (int)((__ldg(&sc.s_c[id]) >> 8) & 0xffu);
+                    type = (int)((__ldg(&sc.s_c[e]) >> 8) & 0xffu);
                 }
+                // A marginal winner (grazed corner, origin on a face, range limit) is not decided here: the ray goes to
+                // k_lidar_fix, which re-traces it with the reference's exact clip over every box. (Doing the exact clip
+                // here, and the re-trace as a call, cost every agent up to 25 % more time - 9.2 vs 7.7 ms per launch -
+                // for a path that about one ray in 200 000 takes.)
+                retrace = (id & 0x8000u) != 0;
+                GD_CNT(13, retrace ? 1 : 0);
                 const float2 d = wp.v.g.raydir[i % NRAY];
 #ifdef GD_OBS_FULL_EXACT
-                const float te = ray_box_exact(px, py, bx, by, bqw, bqz, d0, d1, d.x, d.y);
+                t = ray_box_exact(px, py, bx, by, bqw, bqz, d0, d1, d.x, d.y);
 #else
-                const float te = ray_box_exact_depth(px, py, bx, by, bqw, bqz, d0, d1, d.x, d.y);
+                t = ray_box_exact_depth(px, py, bx, by, bqw, bqz, d0, d1, d.x, d.y);
 #endif
-                if (te >= 0.f) t = te;      // (a grazing ray may flip to a miss in exact arithmetic: keep the fast t)
                 const float2 xy = wp.v.g.rayxy[i % NRAY];
                 v = make_float4(t, (float)type, __fmul_rn(t, xy.x), __fmul_rn(t, xy.y));
             }
-            out[i] = v;
+            if (!retrace) out[i] = v;
+            else {
+                const unsigned slot = atomicAdd(&st.retrace[0], 1u);
+                if (slot < kRetraceCap) st.retrace[1 + slot] = (unsigned)(wa * (3 * NRAY) + i);
+            }
         }
         __syncwarp();
     }

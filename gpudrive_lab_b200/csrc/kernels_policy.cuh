@@ -15,12 +15,22 @@ namespace gd {
 
 constexpr int kPolicyEgo = 6, kPolicyPartner = 6, kPolicyRoad = 13;
 
+// `tensor / python_scalar` in torch: an IEEE division on the CPU; on CUDA the tensor times the float reciprocal of the
+// scalar (ATen/native/cuda/BinaryDivTrueKernel.cu: "a * reciprocal(b) ... may lose one bit"). The env's get_obs()
+// runs on whichever device it was given, so both arithmetics exist: normalize = 1 reproduces the CPU path (what
+// the golden vectors pin), normalize = 2 the CUDA path, each bit for bit.
+template <bool RCP>
+__device__ __forceinline__ float tdiv(float v, float c) {
+    return RCP ? __fmul_rn(v, __fdiv_rn(1.f, c)) : __fdiv_rn(v, c);
+}
+template <bool RCP>
 __device__ __forceinline__ float norm_min_max(float v) {      // normalize_min_max(v, -1000, 1000)
-    return __fsub_rn(__fmul_rn(2.f, __fdiv_rn(__fsub_rn(v, -1000.f), 2000.f)), 1.f);
+    return __fsub_rn(__fmul_rn(2.f, tdiv<RCP>(__fsub_rn(v, -1000.f), 2000.f)), 1.f);
 }
 
 // One CTA per agent slot. Inputs are read and the output written with fully coalesced accesses; the row
 // arithmetic happens between two shared-memory images (needs S <= 128: the engine's limit).
+template <bool RCP>
 __global__ void __launch_bounds__(256)
 k_policy_obs(Exports ex, float *__restrict__ out, int S, int normalize)
 {
@@ -43,33 +53,33 @@ k_policy_obs(Exports ex, float *__restrict__ out, int S, int normalize)
     const float scale = 0.7f;                       // madrona_gpudrive.vehicleScale
     if (tid == 0) {                                 // speed, length, width, goal x, goal y, collided
         const float len = __fmul_rn(s_in[1], scale), wid = __fmul_rn(s_in[2], scale);
-        s_out[0] = normalize ? __fdiv_rn(s_in[0], 100.f) : s_in[0];
-        s_out[1] = normalize ? __fdiv_rn(len, 30.f) : len;
-        s_out[2] = normalize ? __fdiv_rn(wid, 15.f) : wid;
-        s_out[3] = normalize ? norm_min_max(s_in[4]) : s_in[4];
-        s_out[4] = normalize ? norm_min_max(s_in[5]) : s_in[5];
+        s_out[0] = normalize ? tdiv<RCP>(s_in[0], 100.f) : s_in[0];
+        s_out[1] = normalize ? tdiv<RCP>(len, 30.f) : len;
+        s_out[2] = normalize ? tdiv<RCP>(wid, 15.f) : wid;
+        s_out[3] = normalize ? norm_min_max<RCP>(s_in[4]) : s_in[4];
+        s_out[4] = normalize ? norm_min_max<RCP>(s_in[5]) : s_in[5];
         s_out[5] = s_in[6];
     }
     if (tid < P) {                                  // speed, x, y, heading, length, width
         const float *r = s_po + tid * kPartnerObsSize;
         float *o = s_out + kPolicyEgo + tid * kPolicyPartner;
         const float len = __fmul_rn(r[4], scale), wid = __fmul_rn(r[5], scale);
-        o[0] = normalize ? __fdiv_rn(r[0], 100.f) : r[0];
-        o[1] = normalize ? norm_min_max(r[1]) : r[1];
-        o[2] = normalize ? norm_min_max(r[2]) : r[2];
-        o[3] = normalize ? __fdiv_rn(r[3], two_pi) : r[3];
-        o[4] = normalize ? __fdiv_rn(len, 30.f) : len;
-        o[5] = normalize ? __fdiv_rn(wid, 15.f) : wid;
+        o[0] = normalize ? tdiv<RCP>(r[0], 100.f) : r[0];
+        o[1] = normalize ? norm_min_max<RCP>(r[1]) : r[1];
+        o[2] = normalize ? norm_min_max<RCP>(r[2]) : r[2];
+        o[3] = normalize ? tdiv<RCP>(r[3], two_pi) : r[3];
+        o[4] = normalize ? tdiv<RCP>(len, 30.f) : len;
+        o[5] = normalize ? tdiv<RCP>(wid, 15.f) : wid;
     }
     if (tid < kMaxAgentMapObs) {                    // x, y, d0, d1, d2, heading, one_hot7(type)
         const float *r = s_ro + tid * kMapObsSize;
         float *o = s_out + kPolicyEgo + P * kPolicyPartner + tid * kPolicyRoad;
-        o[0] = normalize ? norm_min_max(r[0]) : r[0];
-        o[1] = normalize ? norm_min_max(r[1]) : r[1];
-        o[2] = normalize ? __fdiv_rn(r[2], 100.f) : r[2];
-        o[3] = normalize ? __fdiv_rn(r[3], 100.f) : r[3];
-        o[4] = normalize ? __fdiv_rn(r[4], 100.f) : r[4];
-        o[5] = normalize ? __fdiv_rn(r[5], two_pi) : r[5];
+        o[0] = normalize ? norm_min_max<RCP>(r[0]) : r[0];
+        o[1] = normalize ? norm_min_max<RCP>(r[1]) : r[1];
+        o[2] = normalize ? tdiv<RCP>(r[2], 100.f) : r[2];
+        o[3] = normalize ? tdiv<RCP>(r[3], 100.f) : r[3];
+        o[4] = normalize ? tdiv<RCP>(r[4], 100.f) : r[4];
+        o[5] = normalize ? tdiv<RCP>(r[5], two_pi) : r[5];
         const int ty = (int)r[6];
 #pragma unroll
         for (int k = 0; k < 7; k++) o[6 + k] = ty == k ? 1.f : 0.f;

@@ -59,6 +59,7 @@ k_agents(const SceneDev *__restrict__ scenes, StateDev st, Exports ex, Params pr
     // episode statistics of this world's step (gd_stats): 0 -> 1 transitions of the Info / Done flags
     __shared__ unsigned s_cnt[ST_NUM];
     if (threadIdx.x < ST_NUM) s_cnt[threadIdx.x] = 0;
+    if (blockIdx.x == 0 && threadIdx.x == 0) st.retrace[0] = 0;     // k_obs -> k_lidar_fix hand-off list of this step
 
     const int w = blockIdx.x;
     if (only_flagged && !st.reset_flag[w]) return;      // auto-reset: only the worlds that were just re-bound

@@ -241,11 +241,14 @@ class SimManager:
         _capi.check(self._lib.gd_kernel_times(self._h, C.byref(a), C.byref(o), C.byref(n)))
         return {"k_agents_ms": a.value, "k_obs_ms": o.value, "steps": n.value}
 
-    def policy_observation_tensor(self, normalize=True) -> Tensor:
+    def policy_observation_tensor(self, normalize=True, torch_cuda_arithmetic=False) -> Tensor:
         """Flat policy observation [W, S, 6 + (S-1)*6 + 200*13] (GPUDriveTorchEnv.get_obs defaults), computed on
-        the device from the current exports; recomputed at every call."""
+        the device from the current exports; recomputed at every call. torch divides a tensor by a Python scalar
+        exactly on the CPU and by multiplying with the float reciprocal on CUDA: torch_cuda_arithmetic selects
+        which of the two get_obs() results is reproduced bit for bit (default: the CPU one, pinned by goldens)."""
         d = _capi.GdTensorDesc()
-        _capi.check(self._lib.gd_policy_obs(self._h, 1 if normalize else 0, C.byref(d)))
+        mode = 0 if not normalize else (2 if torch_cuda_arithmetic else 1)
+        _capi.check(self._lib.gd_policy_obs(self._h, mode, C.byref(d)))
         return Tensor(d, self)
 
     _REWARD_MODES = {"sparse_on_goal_achieved": 0, "weighted_combination": 1, "reward_conditioned": 2,

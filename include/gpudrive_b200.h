@@ -140,7 +140,10 @@ int gd_step_host(GdHandle h, const float *actions, int32_t action_cols, float *r
 /* Flat policy observation of every agent slot, computed on the device from the current exports in one pass:
  * what GPUDriveTorchEnv.get_obs() builds in Python with the default ego_state + partner_obs + road_map_obs
  * (gpudrive/env/env_torch.py:756-891,1172-1216; normalisation constants gpudrive/env/constants.py).
- * out: f32 [W, S, 6 + (S-1)*6 + 200*13], valid until the next call. normalize = config.norm_obs. */
+ * out: f32 [W, S, 6 + (S-1)*6 + 200*13], valid until the next call. normalize: 0 = raw (config.norm_obs off),
+ * 1 = normalised with torch's CPU arithmetic (`x / c` is an IEEE division), 2 = normalised with torch's CUDA
+ * arithmetic (`x / c` is x times the float reciprocal of c, ATen BinaryDivTrueKernel.cu) - bit-identical to what
+ * get_obs() returns with device="cpu" / device="cuda" respectively. */
 int gd_policy_obs(GdHandle h, int32_t normalize, GdTensorDesc *out);
 /* Shaped reward of every agent slot, computed on the device from info / reward / expert_trajectory /
  * absolute_self_observation in one pass: GPUDriveTorchEnv.get_rewards (gpudrive/env/env_torch.py:469-604).

@@ -18,7 +18,9 @@ int main(int argc, char **argv) {
             volatile float vx = x;     // keep the compiler from folding the libm calls
             float s = sinf(vx), c = cosf(vx), s2, c2;
             sincosf(vx, &s2, &c2);
-            float ms = gdtrig::sinf_glibc(x), mc = gdtrig::cosf_glibc(x);
+            float ms = gdtrig::sinf_glibc(x), mc = gdtrig::cosf_glibc(x), qs, qc;
+            gdtrig::sincosf_glibc(x, qs, qc);      // the one-pass form the lidar ray directions use
+            if (bits(qs) != bits(s) || bits(qc) != bits(c)) { if (bad_sc++ < 5) printf("sincosf_glibc(%a): %a %a vs libm %a %a\n", x, qs, qc, s, c); }
             n++;
             if (bits(s) != bits(ms)) { if (bad_s++ < 5) printf("sin(%a): libm %a mine %a\n", x, s, ms); }
             if (bits(c) != bits(mc)) { if (bad_c++ < 5) printf("cos(%a): libm %a mine %a\n", x, c, mc); }

@@ -147,7 +147,7 @@ def test_reference_env_runs_unchanged_on_the_engine(synth_dir):
     assert not np.array_equal(out["obs_after_swap"], out["obs"][0])   # the second batch of scenes
     # get_obs() of the reference env == the engine's device-side policy observation, bit for bit
     want = env.get_obs()
-    got = sim.policy_observation_tensor(normalize=True).to_torch()
+    got = sim.policy_observation_tensor(normalize=True, torch_cuda_arithmetic=True).to_torch()   # env device = "cuda"
     assert got.shape == want.shape
     assert torch.equal(got.view(torch.int32), want.contiguous().view(torch.int32))
     # get_rewards() == gd_shaped_reward

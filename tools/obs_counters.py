@@ -1,15 +1,11 @@
 """Kernel experiment: per-agent work counters of k_obs (needs a library built with -DGD_COUNTERS)."""
 import ctypes as C, os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
-sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tests"))
 import torch
-import bench
-from helpers import engine_params
-from gpudrive_lab_b200 import madrona_gpudrive as mg, _capi
+from gpudrive_lab_b200 import madrona_gpudrive as mg, _capi, workload as wl
 W = int(sys.argv[1]) if len(sys.argv) > 1 else 256
-scenes_u = bench.make_scenes(bench.UNIQUE_SCENES)
-scenes = [scenes_u[i % len(scenes_u)] for i in range(W)]
-sim = mg.SimManager(mg.madrona.ExecMode.CUDA, 0, scenes, engine_params(bench.params_dict()), max_agents=128)
+scenes = wl.world_scenes(wl.make_scenes(3), W)
+sim = mg.SimManager(mg.madrona.ExecMode.CUDA, 0, scenes, wl.engine_params(wl.params_dict(3)), max_agents=128)
 lib = _capi.load()
 out = (C.c_ulonglong * 16)()
 act = sim.action_tensor().to_torch()
@@ -21,6 +17,7 @@ sim.step()
 lib.gd_debug_counters(out, 0)
 n = out[0]
 names = ["agents", "groups listed", "groups processed", " with lidar", " with knn", "(box, ray) pairs clipped", "clip-stage calls",
-         "-", "in-radius candidates", "clip rounds", "agents over the candidate cap"]
+         "-", "in-radius candidates", "clip rounds", "agents over the candidate cap", "-", "-",
+         "marginal winners (exact clip)", "rays handed to k_lidar_fix"]
 for i, nm in enumerate(names):
     print(f"{nm:28s} {out[i]:12d}  per agent {out[i] / max(n, 1):9.2f}")
