@@ -61,6 +61,7 @@ EXPORTED_SYMBOLS = [
     "gd_num_worlds", "gd_max_agents", "gd_launch_count", "gd_stream", "gd_last_error",
     "gd_scene_info", "gd_scene_tensors", "gd_scene_road_pose", "gd_policy_obs", "gd_set_option", "gd_kernel_times",
     "gd_pool_convert", "gd_pool_count", "gd_shaped_reward", "gd_expert_actions", "gd_auto_reset_pool", "gd_auto_reset",
+    "gd_scatter_actions_noalloc",
 ]
 
 TENSOR_IDS = {
@@ -100,6 +101,7 @@ def load():
     lib.gd_bind_worlds.argtypes = [H, C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.c_int32]
     lib.gd_auto_reset_pool.argtypes = [H, C.POINTER(C.c_int32), C.c_int32]
     lib.gd_auto_reset.argtypes = [H]
+    lib.gd_scatter_actions_noalloc.argtypes = [C.c_void_p, C.c_int64, C.c_int32, C.c_void_p, C.c_uint64]
     lib.gd_shaped_reward.argtypes = [H, C.POINTER(GdRewardShaping), C.POINTER(GdTensorDesc)]
     lib.gd_expert_actions.argtypes = [H, C.POINTER(GdTensorDesc)]
     lib.gd_pool_convert.argtypes = [C.POINTER(C.c_char_p), C.c_int32, C.c_float, C.c_char_p, C.c_int32]

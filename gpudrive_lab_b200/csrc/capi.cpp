@@ -12,6 +12,11 @@
 
 static thread_local std::string g_last_error;
 
+namespace gd {
+// for entry points that live in the CUDA translation unit (engine.cu): same per-thread message as GD_TRY's
+void setLastError(const std::string &msg) { g_last_error = msg; }
+}
+
 static_assert(sizeof(GdParams) == sizeof(gd::Params), "GdParams and gd::Params must match");
 static_assert(sizeof(GdTensorDesc) == sizeof(gd::TensorDesc), "tensor desc mismatch");
 static_assert((int)GD_T_COUNT == (int)gd::T_NUM, "tensor id tables out of sync");

@@ -889,6 +889,57 @@ TensorDesc Engine::tensor(int id) const {
 
 } // namespace gd
 
+// ------------------------------------------------------------------------------------------------------------
+// gd_scatter_actions_noalloc (include/gpudrive_b200.h): the action staging of gd_step_host - contiguous
+// [n_rows, cols] actions -> a landing buffer -> k_scatter_actions -> the first `cols` columns of [n_rows, 10] action
+// rows - with the landing buffer in this file-scope device array instead of cudaMalloc'ed memory, for callers that
+// must not allocate (CUDA graph capture, tight serving loops). No counterpart in the reference.
+// Every GPU that loads the library holds the array (16 MiB) until exit.
+// In host code `g_noalloc_stage` is only a stand-in for the symbol, not a device address: the address is resolved
+// once per device with cudaGetSymbolAddress (below) and that pointer is what the copy and the kernel get.
+// ------------------------------------------------------------------------------------------------------------
+namespace gd {
+void setLastError(const std::string &msg);          // capi.cpp
+constexpr size_t kNoAllocMaxFloats = size_t(4) << 20;         // 4 Mi floats = 16 MiB
+static __device__ __align__(256) float g_noalloc_stage[kNoAllocMaxFloats];
+constexpr int kNoAllocMaxDevices = 64;
+static float *g_noalloc_ptr[kNoAllocMaxDevices];              // per device: device address of g_noalloc_stage
+}
+
+extern "C" int gd_scatter_actions_noalloc(const float *actions, int64_t n_rows, int32_t action_cols,
+                                          float *action_rows_out, uint64_t stream)
+{
+    using namespace gd;
+    auto fail = [](const std::string &m) { setLastError("gd_scatter_actions_noalloc: " + m); return 1; };
+    if (!actions || !action_rows_out) return fail("null pointer");
+    if (action_cols <= 0 || action_cols > kActionSize) return fail("action_cols must be in [1, 10]");
+    if (n_rows < 0) return fail("negative row count");
+    const unsigned long long n = (unsigned long long)n_rows * (unsigned long long)action_cols;
+    if (n > kNoAllocMaxFloats)
+        return fail("n_rows * action_cols = " + std::to_string(n) + " floats exceeds the static staging array's maximum of " +
+                    std::to_string(kNoAllocMaxFloats) + " floats (16 MiB); split the call or use gd_step_host");
+    if (n == 0) return 0;
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return fail(std::string("cudaGetDevice: ") + cudaGetErrorString(e));
+    if (dev < 0 || dev >= kNoAllocMaxDevices) return fail("device ordinal out of range");
+    if (!g_noalloc_ptr[dev]) {       // set-up, once per device, with that device current
+        float *p = nullptr;
+        e = cudaGetSymbolAddress((void **)&p, g_noalloc_stage);
+        if (e != cudaSuccess || !p) return fail(std::string("cudaGetSymbolAddress: ") + cudaGetErrorString(e));
+        g_noalloc_ptr[dev] = p;
+    }
+    float *stage = g_noalloc_ptr[dev];
+    cudaStream_t st = (cudaStream_t)(uintptr_t)stream;
+    // (nothing in the array has to start at zero: the kernel reads exactly the n floats this call wrote)
+    e = cudaMemcpyAsync(stage, actions, n * sizeof(float), cudaMemcpyDefault, st);
+    if (e != cudaSuccess) return fail(std::string("cudaMemcpyAsync: ") + cudaGetErrorString(e));
+    k_scatter_actions<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(stage, action_cols, action_rows_out, (size_t)n);
+    e = cudaGetLastError();
+    if (e != cudaSuccess) return fail(std::string("kernel launch: ") + cudaGetErrorString(e));
+    return 0;
+}
+
 #ifdef GD_COUNTERS
 extern "C" int gd_debug_counters(unsigned long long *out, int reset) {
     cudaDeviceSynchronize();

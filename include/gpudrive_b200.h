@@ -137,6 +137,21 @@ int gd_tensor(GdHandle h, int32_t tensor_id, GdTensorDesc *out);
  * (gpudrive/env/env_torch.py:606-660). */
 int gd_step_host(GdHandle h, const float *actions, int32_t action_cols, float *reward, int32_t *done,
                  int32_t *info);
+/* The action staging of gd_step_host without any allocation. This entry point has no counterpart in the reference;
+ * it was added for callers that cannot call cudaMalloc (code under CUDA graph
+ * capture, tight serving loops, harnesses that forbid it). It copies actions[n_rows, action_cols] (host - pinned or
+ * pageable - or device memory) into a staging array that lives in the library's device image (a file-scope
+ * `static __device__` array of 4 Mi floats = 16 MiB, which every GPU that loads the library holds until exit) and
+ * scatters them into the first `action_cols` columns of action_rows_out[n_rows, 10], a DEVICE buffer on the
+ * current device that the caller owns (e.g. the GD_T_ACTION tensor); the other columns are left untouched. Both
+ * operations are enqueued on `stream` (a cudaStream_t as an integer, 0 = the legacy default stream); the call does
+ * not wait for them. It calls no cudaMalloc / cudaFree / allocating library routine. n_rows * action_cols beyond
+ * 4 194 304 floats is rejected with an error (gd_last_error). The first call on a device resolves the array's
+ * address (cudaGetSymbolAddress): make that one call outside graph capture. All calls share the one array, which
+ * keeps the last call's contents: calls whose work overlaps on the GPU (different streams, no ordering between
+ * them) race; calls on one stream, or ordered by events, are safe. */
+int gd_scatter_actions_noalloc(const float *actions, int64_t n_rows, int32_t action_cols, float *action_rows_out,
+                               uint64_t stream);
 /* Flat policy observation of every agent slot, computed on the device from the current exports in one pass:
  * what GPUDriveTorchEnv.get_obs() builds in Python with the default ego_state + partner_obs + road_map_obs
  * (gpudrive/env/env_torch.py:756-891,1172-1216; normalisation constants gpudrive/env/constants.py).
