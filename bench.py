@@ -290,9 +290,10 @@ def main_engine(args):
 
     all_worlds = list(range(W))
     step_no = [0]
+    episode_steps = c.get("episode_steps", 91)
 
     def one_step(k):
-        if not auto_reset and step_no[0] == 91:   # episode boundary: reset inside the timed region (time, not a step)
+        if not auto_reset and step_no[0] == episode_steps:   # episode boundary: reset inside the timed region (time, not a step)
             sim.reset(all_worlds)
             step_no[0] = 0
         with torch.cuda.stream(stream):
@@ -335,17 +336,20 @@ def main_engine(args):
     h_rew = torch.empty(W, SLOTS, 1).pin_memory()
     h_done = torch.empty(W, SLOTS, 1, dtype=torch.int32).pin_memory()
     h_info = torch.empty(W, SLOTS, 5, dtype=torch.int32).pin_memory()
-    if not auto_reset and step_no[0] + e2e_steps + 1 > 91:
+    if not auto_reset:
         sim.reset(all_worlds); step_no[0] = 0
 
     def e2e_step():
+        if not auto_reset and step_no[0] == episode_steps:
+            sim.reset(all_worlds); step_no[0] = 0
+        step_no[0] += 1
         sim.step_host(h_act, h_rew, h_done, h_info)
         if auto_reset:
             sim.auto_reset()
             sim.policy_observation_tensor()
         return float(h_rew[0, 0, 0])
 
-    e2e_step(); step_no[0] += 1
+    e2e_step()
     barrier()
     t0 = time.perf_counter()
     for k in range(e2e_steps):
@@ -353,7 +357,6 @@ def main_engine(args):
     sim.sync()
     barrier()
     e2e_s = time.perf_counter() - t0
-    step_no[0] += e2e_steps
 
     # ---- reduce over ranks: max time, summed agent counts
     sat = float(stats1["sat_tests"] - stats0["sat_tests"])
