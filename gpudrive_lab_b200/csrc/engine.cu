@@ -136,6 +136,7 @@ void Engine::allocExports() {
     ex_.knn_idx = devAlloc<int32_t>(owned_, WS * kMaxAgentMapObs, 0xff);
     st_.pos = devAlloc<float4>(owned_, WS);
     st_.rv = devAlloc<float4>(owned_, WS);
+    st_.yaw = devAlloc<float>(owned_, WS);
     st_.collided = devAlloc<int32_t>(owned_, WS);
     st_.world_scene = devAlloc<int32_t>(owned_, W_);
     st_.reset_flag = devAlloc<int32_t>(owned_, W_);

@@ -81,6 +81,7 @@ struct Exports {
 struct StateDev {
     float4 *pos;          // [W,S] x, y, z, vz
     float4 *rv;           // [W,S] qw, qz, vx, vy
+    float *yaw;           // [W,S] utils::quatToYaw of the agent's rotation, written by k_agents (fp64 atan2, once per step)
     int32_t *collided;    // [W,S] CollisionDetectionEvent.hasCollided
     int32_t *world_scene; // [W]
     int32_t *reset_flag;  // [W]

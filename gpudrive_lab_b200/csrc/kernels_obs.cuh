@@ -276,14 +276,22 @@ __device__ __forceinline__ int plane_mask(float pz, float bz, float d2, float zm
 {
     int m = 0;
     const float offs[3] = {kLidarCarOffset, kLidarRoadEdgeOffset, kLidarRoadLineOffset};
+    const float inv = rcp_fast(d2);
 #pragma unroll
     for (int p = 0; p < 3; p++) {
         const float oz = __fadd_rn(pz, offs[p]);
-        // 0 / d2 is 0, but a zero operand sends IEEE division down its slow path - and a plane at exactly the
-        // box's height is the common case (1 + 0.1 - 1.1), so it is special-cased
+        // The reference tests lz = (oz - bz) / d2 against the slab [zmin, zmax] (touching counts as inside). Float
+        // subtraction never flips a sign, so that is zmin <= lz <= zmax, and an approximate quotient decides it
+        // unless lz is within 1e-5 of a face: only then is the IEEE division evaluated (and never with a zero
+        // operand, which sends it down its slow path - a plane at exactly the box's height is the common case).
         const float num = __fsub_rn(oz, bz);
-        const float lz = num == 0.f ? 0.f : __fdiv_rn(num == 0.f ? 1.f : num, d2);
-        const bool in = !(__fsub_rn(zmax_obj, lz) < 0.f) && !(__fsub_rn(lz, zmin_obj) < 0.f);
+        const float q = num * inv;
+        bool in = q >= zmin_obj && q <= zmax_obj;
+        const float tol = 1e-5f * fmaxf(1.f, fabsf(q));
+        if (fabsf(q - zmin_obj) <= tol || fabsf(q - zmax_obj) <= tol) {
+            const float lz = num == 0.f ? 0.f : __fdiv_rn(num, d2);
+            in = !(__fsub_rn(zmax_obj, lz) < 0.f) && !(__fsub_rn(lz, zmin_obj) < 0.f);
+        }
         m |= in ? (1 << p) : 0;
     }
     return m;

@@ -66,7 +66,7 @@ k_obs(const SceneDev *__restrict__ scenes, StateDev st, Exports ex, Params prm, 
         ab[0] = make_float2(px, py);
         ab[1] = make_float2(pz, qw);
         ab[2] = make_float2(0.f * qz, 0.f * qz);            // Quat x, y = normal.{x,y} * sinhalf
-        ab[3] = make_float2(qz, quat_to_yaw_hp(qw, qz));
+        ab[3] = make_float2(qz, st.yaw[wa]);                // quatToYaw(rot), computed once per step in k_agents
         ab[4] = make_float2(gc.x, gc.y);
         ab[5] = make_float2(s3.x, s3.y);
         ab[6] = make_float2(s3.z, s1.w);
@@ -146,7 +146,7 @@ k_obs(const SceneDev *__restrict__ scenes, StateDev st, Exports ex, Params prm, 
             wp.v.g.raydir[i] = make_float2(__fmul_rn(dx, inv), __fmul_rn(dy, inv));
             wp.v.g.rayxy[i] = make_float2(x, y);
         }
-        const float yaw = quat_to_yaw(qw, qz);
+        const float yaw = st.yaw[wa];
         const float delta = (2.f * kLidarAngle) / (float)NRAY;
         const float mid = yaw + head - kLidarAngle + 0.5f * (float)(NRAY - 1) * delta;
         sincosf(mid, &lc.fs, &lc.fc);
@@ -285,16 +285,19 @@ k_obs(const SceneDev *__restrict__ scenes, StateDev st, Exports ex, Params prm, 
                         cnt += __popc(inm);
                     }
                     if (do_l) {
-                        const int pm = (zmask_classes >> (3 * (int)(c & 0xffu))) & 7;
+                        // a group holds one z-class, so its plane mask and the open rays of those planes are the same
+                        // for all 32 boxes (warp-uniform, from the descriptor); a dummy slot is far away: never alive
+                        const int pm = (int)(gdesc >> 28);
+                        const unsigned long long om = open_for(open, pm);
                         const float relx = ra.x - px, rely = ra.y - py;
                         const float cphi = 1.f - 2.f * ra.w * ra.w, sphi = 2.f * ra.z * ra.w;
                         // cheap tests first: about one pass in five has no box left after them
                         const BoxCull bc = lidar_cull(lc, relx, rely, cphi, sphi, rb.x, rb.y);
-                        if (__any_sync(FULL, pm != 0 && bc.alive)) {
+                        if (__any_sync(FULL, bc.alive)) {
                             int lo, hi;
                             const bool some = lidar_range(bc, lo, hi);
                             // trim the range to its first / last open ray (closed rays inside are clipped too)
-                            const unsigned long long m = (pm && some) ? (ray_bits(lo, hi) & open_for(open, pm)) : 0ull;
+                            const unsigned long long m = some ? (ray_bits(lo, hi) & om) : 0ull;
                             lo = m ? __ffsll((long long)m) - 1 : 0;
                             const int n = m ? 64 - __clzll((long long)m) - lo : 0;
                             lidar_expand(wp, lane, lo, n, pm, (unsigned)e, relx, rely, cphi, sphi, rb.x, rb.y);
@@ -332,7 +335,7 @@ k_obs(const SceneDev *__restrict__ scenes, StateDev st, Exports ex, Params prm, 
                 // A marginal winner (grazed corner, origin on a face, range limit) is not decided here: the ray goes to
                 // k_lidar_fix, which re-traces it with the reference's exact clip over every box. (Doing the exact clip
                 // here, and the re-trace as a call, cost every agent up to 25 % more time - 9.2 vs 7.7 ms per launch -
-                // for a path that about one ray in 200 000 takes.)
+                // for a path that about one ray in 2 500 takes.)
                 retrace = (id & 0x8000u) != 0;
                 GD_CNT(13, retrace ? 1 : 0);
                 const float2 d = wp.v.g.raydir[i % NRAY];
@@ -408,6 +411,7 @@ k_obs(const SceneDev *__restrict__ scenes, StateDev st, Exports ex, Params prm, 
         inbin = __shfl_sync(FULL, inbin, src);
     };
 
+#ifndef GD_OBS_LEAN
     if (cnt > OBS_CAND) {
         // Dense map: more in-radius entities than the candidate buffer holds (a 10 000-entity scene has ~900 within
         // 50 m). Two more sweeps over the near groups only: a histogram of the quantised keys finds the bin of the
@@ -455,7 +459,12 @@ k_obs(const SceneDev *__restrict__ scenes, StateDev st, Exports ex, Params prm, 
             __syncwarp();
         }
     }
+#endif
+#ifdef GD_OBS_LEAN
+    const bool overflow = false;
+#else
     const bool overflow = cnt > OBS_CAND;
+#endif
     const int C = min(cnt, OBS_CAND);
     const bool take_all = cnt <= K;
     const int N = overflow ? RS : C;
@@ -499,6 +508,7 @@ k_obs(const SceneDev *__restrict__ scenes, StateDev st, Exports ex, Params prm, 
             __syncwarp();
         }
     }
+#ifndef GD_OBS_LEAN
     if (!selected) {
         // general path (candidate overflow, or many equal keys): exact radix select (4 x 8 bits, MSB first)
         // of the K-th smallest key among in-radius entities
@@ -569,6 +579,7 @@ k_obs(const SceneDev *__restrict__ scenes, StateDev st, Exports ex, Params prm, 
         }
     }
 
+#endif
     // One chunk of 32 candidates: is entry i selected, and which sorted slot / road word does it carry?
     auto candidate = [&](int i, int &e, uint32_t &rc) -> bool {
         bool acc = false; unsigned kb = 0;
@@ -592,6 +603,7 @@ k_obs(const SceneDev *__restrict__ scenes, StateDev st, Exports ex, Params prm, 
         row[5] = quat_to_yaw(rw, rz); row[6] = (float)((rc >> 8) & 0xffu); row[7] = rd.z; row[8] = rd.w;
     };
 
+#ifndef GD_OBS_LEAN
     if (first_k_only) {
         // Linear algorithm: the reference emits the first K in-radius entities in road-index order
         // (sim.cpp:261-279), so the order is part of the contract. The selected road indices go into a bit map
@@ -647,7 +659,9 @@ k_obs(const SceneDev *__restrict__ scenes, StateDev st, Exports ex, Params prm, 
         const int n = (K - emitted) * 9;
         float *dst = rows + (size_t)emitted * 9;
         for (int i = lane; i < n; i += 32) dst[i] = (i % 9) >= 7 ? -1.f : 0.f;
-    } else {
+    } else
+#endif
+    {
         // k-nearest: the reference leaves the rows in heap order; here by distance band, then by sorted slot
         for (int base = 0; base < N && emitted < K; base += 32) {
             int e; uint32_t rc;

@@ -173,6 +173,7 @@ k_agents(const SceneDev *__restrict__ scenes, StateDev st, Exports ex, Params pr
         // ---- box for phase B
         AgentBox &bx = box[a];
         const float yaw = quat_to_yaw_hp(rv.x, rv.y);
+        st.yaw[wa] = yaw;                  // k_obs exports it (AbsoluteSelfObservation) and aims the lidar fan with it
         const float c = cos_hp(yaw), s = sin_hp(yaw);
         obb_from(p.x, p.y, c, s, agb.x, agb.y, bx.obb);
         bx.cx = p.x; bx.cy = p.y;
