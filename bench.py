@@ -255,6 +255,8 @@ def main_engine(args):
     if auto_reset:
         sim.auto_reset_pool([sim.pool_add(p) for p in scenes_u])
         sim.set_option(3, 1)    # the policy observation is consumed on the device: no host wait per step
+        if not args.separate_policy_obs:
+            sim.set_option(4, 1)   # k_obs writes the policy observation itself (GD_OPT_FUSED_POLICY_OBS)
     stream = torch.cuda.ExternalStream(sim.cuda_stream(), device=local_rank)
     shape = sim.shape_tensor().to_torch()
     ctrl_t = sim.controlled_state_tensor().to_torch()
@@ -301,7 +303,7 @@ def main_engine(args):
         sim.step_async()
         if auto_reset:
             sim.auto_reset()
-            sim.policy_observation_tensor()       # the rollout's read-out, on the device
+            sim.policy_observation_tensor(torch_cuda_arithmetic=True)     # the rollout's read-out, on the device
         step_no[0] += 1
 
     for k in range(args.warmup):
@@ -346,7 +348,7 @@ def main_engine(args):
         sim.step_host(h_act, h_rew, h_done, h_info)
         if auto_reset:
             sim.auto_reset()
-            sim.policy_observation_tensor()
+            sim.policy_observation_tensor(torch_cuda_arithmetic=True)
         return float(h_rew[0, 0, 0])
 
     e2e_step()
@@ -368,7 +370,9 @@ def main_engine(args):
         value = tot_ctrl * args.steps / (ms_total * 1e-3)
         e2e_value = tot_ctrl * e2e_steps / e2e_s
         peak, peak_src = measured_peak_gbs()
-        b_step, b_obs = wl.algorithmic_bytes(SLOTS, R_mean, c["agents"], bool(pd["enableLidar"]))
+        fused_pol = auto_reset and not args.separate_policy_obs        # k_obs then also writes 3 368 floats per agent
+        b_step, b_obs = wl.algorithmic_bytes(SLOTS, R_mean, c["agents"], bool(pd["enableLidar"]),
+                                             policy_obs_floats=(6 + (SLOTS - 1) * 6 + wl.K_ROAD * 13) if fused_pol else 0)
         obs_ms = kt["k_obs_ms"] / max(kt["steps"], 1)
         agents_ms = kt["k_agents_ms"] / max(kt["steps"], 1)
         achieved = b_obs * n_live / (obs_ms * 1e-3) / 1e9 if obs_ms > 0 else 0.0
@@ -425,6 +429,8 @@ def main():
     ap.add_argument("--unique-scenes", type=int, default=0, help="distinct scenarios per job (default: the config's)")
     ap.add_argument("--budget", type=float, default=60.0, help="reference arm: seconds of CPU work to sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--separate-policy-obs", action="store_true",
+                    help="config 4: compute the policy observation in its own pass instead of as k_obs' second output")
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "engine":
         args.warmup = 3

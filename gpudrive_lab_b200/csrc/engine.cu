@@ -79,7 +79,8 @@ Engine::Engine(int gpu_id, int max_agents, const Params &params, const std::vect
     for (int w = 0; w < W_; w++) world_scene_[w] = sceneFor(scenes[w], deleted_[w]);
     GD_CUDA(cudaMemcpy(st_.world_scene, world_scene_.data(), W_ * sizeof(int32_t), cudaMemcpyHostToDevice));
 
-    GD_CUDA(cudaFuncSetAttribute(k_obs, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(ObsSmem)));
+    GD_CUDA(cudaFuncSetAttribute(k_obs<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(ObsSmem)));
+    GD_CUDA(cudaFuncSetAttribute(k_obs<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(ObsSmem)));
     if (bev_enabled_)
         GD_CUDA(cudaFuncSetAttribute(k_bev, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(BevSmem)));
 
@@ -461,7 +462,7 @@ void Engine::launchBindReset(const std::vector<int32_t> &worlds, bool rebind, bo
         launches_++;
     }
     if (rebind) {
-        k_bind<<<dim3(n, BIND_SPLIT), 256, 0, stream_>>>(d_worklist_, d_scenes_, st_, ex_, S_);
+        k_bind<<<dim3(n, BIND_SPLIT), 256, 0, stream_>>>(d_worklist_, d_scenes_, st_, ex_, S_, fusedPolicy());
         launches_++;
     }
     const int blk = ((S_ + 31) / 32) * 32;
@@ -510,6 +511,7 @@ void Engine::buildStepGraph(const StepGraphKey &key) {
     const SceneDev *scenes = d_scenes_;
     int S = S_, one = 1, zero = 0, groups = key.groups, knn = key.knn_idx;
     float key_thr = key_thr_;
+    float *pol = fusedPolicy();
     if (key.profile) add_event(prof_ev_[0], &graph_ev_nodes_[0]);
     {
         void *args[] = {&scenes, &st_, &ex_, &params_, &S, &one, &one, &zero};
@@ -518,8 +520,8 @@ void Engine::buildStepGraph(const StepGraphKey &key) {
     if (key.profile) add_event(prof_ev_[1], &graph_ev_nodes_[1]);
     add_event(ev_agents_, nullptr);         // reward / done / info are final here (stepHost's copy stream waits on it)
     {
-        void *args[] = {&scenes, &st_, &ex_, &params_, &S, &groups, &knn, &key_thr, &zero};
-        add_kernel((void *)k_obs, dim3(W_ * groups), dim3(OBS_BLOCK), sizeof(ObsSmem), args);
+        void *args[] = {&scenes, &st_, &ex_, &params_, &S, &groups, &knn, &key_thr, &zero, &pol};
+        add_kernel(pol ? (void *)k_obs<true> : (void *)k_obs<false>, dim3(W_ * groups), dim3(OBS_BLOCK), sizeof(ObsSmem), args);
     }
     if (params_.enableLidar) {      // the few rays k_obs could not settle, re-traced exactly (counted with k_obs' time)
         void *args[] = {&scenes, &st_, &ex_, &S};
@@ -550,6 +552,7 @@ void Engine::launchRest(bool decrement, bool only_flagged) {
     if (decrement && opt_graph_) {
         StepGraphKey key;
         key.scenes = d_scenes_; key.groups = groups; key.knn_idx = opt_knn_idx_; key.profile = prof ? 1 : 0;
+        key.pol = fusedPolicy();
         if (!graph_exec_ || !(key == graph_key_)) buildStepGraph(key);
         if (prof) {
             for (int i = 0; i < 3; i++)
@@ -565,8 +568,12 @@ void Engine::launchRest(bool decrement, bool only_flagged) {
                                                                     decrement ? 1 : 0, decrement ? 1 : 0, flagged);
     if (prof) GD_CUDA(cudaEventRecord(ev[1], stream_));
     if (mark_agents_done_) GD_CUDA(cudaEventRecord(ev_agents_, stream_));   // reward / done / info are final here
-    k_obs<<<W_ * groups, OBS_BLOCK, sizeof(ObsSmem), stream_>>>(d_scenes_, st_, ex_, params_, S_, groups,
-                                                                opt_knn_idx_, key_thr_, flagged);
+    if (fusedPolicy())
+        k_obs<true><<<W_ * groups, OBS_BLOCK, sizeof(ObsSmem), stream_>>>(d_scenes_, st_, ex_, params_, S_, groups,
+                                                                          opt_knn_idx_, key_thr_, flagged, fusedPolicy());
+    else
+        k_obs<false><<<W_ * groups, OBS_BLOCK, sizeof(ObsSmem), stream_>>>(d_scenes_, st_, ex_, params_, S_, groups,
+                                                                           opt_knn_idx_, key_thr_, flagged, nullptr);
     if (params_.enableLidar) k_lidar_fix<<<FIX_GRID, FIX_BLOCK, 0, stream_>>>(d_scenes_, st_, ex_, S_);
     if (prof) { GD_CUDA(cudaEventRecord(ev[2], stream_)); prof_pending_++; }
     if (bev_enabled_)
@@ -699,7 +706,7 @@ void Engine::autoReset() {
     syncSceneTable();
     k_autoreset_select<<<(W_ * 32 + 255) / 256, 256, 0, stream_>>>(st_, ex_, d_scenes_, d_pool_ids_, n_pool_,
                                                                     d_pool_cursor_, W_, S_);
-    k_bind<<<dim3(W_, BIND_SPLIT), 256, 0, stream_>>>(nullptr, d_scenes_, st_, ex_, S_);
+    k_bind<<<dim3(W_, BIND_SPLIT), 256, 0, stream_>>>(nullptr, d_scenes_, st_, ex_, S_, fusedPolicy());
     const int blk = ((S_ + 31) / 32) * 32;
     k_reset<<<W_, blk, 0, stream_>>>(nullptr, d_scenes_, st_, ex_, S_, params_.dynamicsModel);
     launches_ += 3;
@@ -744,14 +751,23 @@ void Engine::stepHost(const float *actions, int action_cols, float *reward, int3
     sync();
 }
 
+int Engine::policyWidth() const { return kPolicyEgo + (S_ - 1) * kPolicyPartner + kMaxAgentMapObs * kPolicyRoad; }
+
 TensorDesc Engine::policyObs(int normalize) {
     GD_CUDA(cudaSetDevice(gpu_));
-    const int width = kPolicyEgo + (S_ - 1) * kPolicyPartner + kMaxAgentMapObs * kPolicyRoad;
+    const int width = policyWidth();
     if (!d_policy_obs_) d_policy_obs_ = devAlloc<float>(owned_, (size_t)W_ * S_ * width);
-    if (normalize == 2) k_policy_obs<true><<<W_ * S_, 256, 0, stream_>>>(ex_, d_policy_obs_, S_, 1);
-    else k_policy_obs<false><<<W_ * S_, 256, 0, stream_>>>(ex_, d_policy_obs_, S_, normalize ? 1 : 0);
-    launches_++;
-    GD_CUDA(cudaGetLastError());
+    if (opt_fused_policy_ && normalize == 2) {
+        // k_obs has already written it (GD_OPT_FUSED_POLICY_OBS): nothing to launch
+    } else {
+        if (opt_fused_policy_)
+            throw std::runtime_error("policy_obs: with GD_OPT_FUSED_POLICY_OBS the buffer holds the normalised observation in "
+                                     "torch-CUDA arithmetic (normalize = 2); switch the option off for the other forms");
+        if (normalize == 2) k_policy_obs<true><<<W_ * S_, 256, 0, stream_>>>(ex_, d_policy_obs_, S_, 1);
+        else k_policy_obs<false><<<W_ * S_, 256, 0, stream_>>>(ex_, d_policy_obs_, S_, normalize ? 1 : 0);
+        launches_++;
+        GD_CUDA(cudaGetLastError());
+    }
     if (!opt_async_aux_) GD_CUDA(cudaStreamSynchronize(stream_));
     TensorDesc d{};
     d.ptr = d_policy_obs_; d.dtype = 0; d.ndim = 3; d.shape[0] = W_; d.shape[1] = S_; d.shape[2] = width; d.device = gpu_;
@@ -802,6 +818,18 @@ void Engine::setOption(int option, int value) {
         opt_profile_ = value ? 1 : 0;
     } else if (option == 2) opt_graph_ = value ? 1 : 0;
     else if (option == 3) opt_async_aux_ = value ? 1 : 0;
+    else if (option == 4) {
+        GD_CUDA(cudaSetDevice(gpu_));
+        if (value && !opt_fused_policy_) {
+            // from now on k_obs (live slots, every step / reset) and k_bind (padding slots) keep the buffer current;
+            // fill it once from the exports as they stand
+            if (!d_policy_obs_) d_policy_obs_ = devAlloc<float>(owned_, (size_t)W_ * S_ * policyWidth());
+            k_policy_obs<true><<<W_ * S_, 256, 0, stream_>>>(ex_, d_policy_obs_, S_, 1);
+            launches_++;
+            GD_CUDA(cudaGetLastError());
+        }
+        opt_fused_policy_ = value ? 1 : 0;
+    }
     else throw std::runtime_error("unknown option");
 }
 

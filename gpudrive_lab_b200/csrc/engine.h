@@ -148,7 +148,8 @@ public:
     TensorDesc expertActions();
     // options: 0 = write the knn index side buffer (default 1), 1 = per-kernel CUDA-event timing (default 0),
     // 2 = launch a step as one CUDA graph (default 1), 3 = policy_obs / shaped_reward / expert_actions return
-    // without waiting for the device (default 0: they return when the tensor is ready)
+    // without waiting for the device (default 0: they return when the tensor is ready), 4 = k_obs also writes the
+    // flat policy observation (torch-CUDA arithmetic) as a second output (default 0)
     void setOption(int option, int value);
     // accumulated device time of the two step kernels since profiling was switched on (ms) and the step count
     void kernelTimes(double *agents_ms, double *obs_ms, int64_t *steps);
@@ -210,12 +211,12 @@ private:
     int kernels_per_step_ = 0;
     uint64_t launches_ = 0;
     uint64_t steps_ = 0, episodes_reset_ = 0;
-    int opt_knn_idx_ = 1, opt_profile_ = 0, opt_graph_ = 1, opt_async_aux_ = 0;
+    int opt_knn_idx_ = 1, opt_profile_ = 0, opt_graph_ = 1, opt_async_aux_ = 0, opt_fused_policy_ = 0;
     // one step = one graph launch: [ev] k_agents [ev] k_obs [ev] (k_bev); rebuilt when a launch parameter changes
     struct StepGraphKey {
-        const void *scenes = nullptr; int groups = -1, knn_idx = -1, profile = -1;
+        const void *scenes = nullptr; const void *pol = nullptr; int groups = -1, knn_idx = -1, profile = -1;
         bool operator==(const StepGraphKey &o) const {
-            return scenes == o.scenes && groups == o.groups && knn_idx == o.knn_idx && profile == o.profile;
+            return scenes == o.scenes && pol == o.pol && groups == o.groups && knn_idx == o.knn_idx && profile == o.profile;
         }
     };
     StepGraphKey graph_key_;
@@ -225,6 +226,8 @@ private:
     void buildStepGraph(const StepGraphKey &key);
     void destroyStepGraph();
     int obsGroups() const;
+    float *fusedPolicy() const { return opt_fused_policy_ ? d_policy_obs_ : nullptr; }
+    int policyWidth() const;
     float key_thr_ = 0.f;
     static constexpr int kProfRing = 64;
     std::vector<cudaEvent_t> prof_ev_;      // 3 events per ring slot

@@ -19,11 +19,12 @@ __global__ void __launch_bounds__(FIX_BLOCK)
 k_lidar_fix(const SceneDev *__restrict__ scenes, StateDev st, Exports ex, int S)
 {
     __shared__ uint16_t s_list[FIX_WARPS][FIX_LIST];     // boxes the fast clip cannot rule out (0x4000 | agent slot, or road slot)
+    __shared__ uint16_t s_glist[FIX_WARPS][kMaxRoadEntityCount / 32 + 24];   // road groups the ray can reach
     const unsigned FULL = 0xffffffffu;
     const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
     const unsigned lt_mask = (1u << lane) - 1u;
     const int warp = blockIdx.x * FIX_WARPS + wib, nwarps = FIX_GRID * FIX_WARPS;
-    uint16_t *list = s_list[wib];
+    uint16_t *list = s_list[wib], *glist = s_glist[wib];
     const unsigned count = min(st.retrace[0], kRetraceCap);
     for (unsigned it = warp; it < count; it += nwarps) {
         const unsigned code = st.retrace[1 + it];
@@ -86,6 +87,7 @@ k_lidar_fix(const SceneDev *__restrict__ scenes, StateDev st, Exports ex, int S)
             if (nl + __popc(pm) > FIX_LIST) drain();
             if (pass) list[nl + __popc(pm & lt_mask)] = (uint16_t)id;
             nl += __popc(pm);
+            GD_CNT(12, __popc(pm));
         };
         for (int jb = 0; jb < A; jb += 32) {
             const int j = jb + lane;
@@ -101,6 +103,7 @@ k_lidar_fix(const SceneDev *__restrict__ scenes, StateDev st, Exports ex, int S)
         // road groups whose bounding circle the ray can reach (distance of the centre from the ray's line and
         // position along it, with a margin far above the rounding of these few operations), then their boxes
         const int G = sc.numGroups;
+        int ng = 0;
         for (int gb0 = 0; gb0 < G; gb0 += 32) {
             const int g = gb0 + lane;
             bool reach = false;
@@ -112,12 +115,26 @@ k_lidar_fix(const SceneDev *__restrict__ scenes, StateDev st, Exports ex, int S)
                 const float along = fmaf(relx, dx, rely * dy), across = fabsf(fmaf(rely, dx, -(relx * dy)));
                 reach = cm && ((zmask >> (3 * zc + plane)) & 1) && across <= r && along >= -r && along <= kLidarDistance + r;
             }
-            for (unsigned gm = __ballot_sync(FULL, reach); gm; gm &= gm - 1) {
-                const int e = (gb0 + __ffs(gm) - 1) * 32 + lane;
-                const bool valid = (sc.s_c[e] & 0xffu) < (unsigned)sc.numZClasses;         // not a dummy slot
-                const float4 ra = sc.s_a[e]; const float2 rb = sc.s_b[e];
-                consider(valid, (unsigned)e, ra.x, ra.y, ra.z, ra.w, rb.x, rb.y);
+            const unsigned gm = __ballot_sync(FULL, reach);
+            if (reach) glist[ng + __popc(gm & lt_mask)] = (uint16_t)g;
+            ng += __popc(gm);
+        }
+        __syncwarp();
+        GD_CNT(14, 1); GD_CNT(11, ng);
+        // four groups per iteration: their twelve loads are in flight together (the kernel is a chain of dependent
+        // loads; with one group at a time a single ray took 80 us whatever the ray count)
+        for (int gi = 0; gi < ng; gi += 4) {
+            float4 ra[4]; float2 rb[4]; bool valid[4]; int e[4];
+#pragma unroll
+            for (int q = 0; q < 4; q++) {
+                const bool have = gi + q < ng;
+                e[q] = (have ? (int)glist[gi + q] : (int)glist[gi]) * 32 + lane;
+                valid[q] = have && (sc.s_c[e[q]] & 0xffu) < (unsigned)sc.numZClasses;       // not a dummy slot
+                ra[q] = sc.s_a[e[q]]; rb[q] = sc.s_b[e[q]];
             }
+#pragma unroll
+            for (int q = 0; q < 4; q++)
+                if (gi + q < ng) consider(valid[q], (unsigned)e[q], ra[q].x, ra[q].y, ra[q].z, ra[q].w, rb[q].x, rb[q].y);
         }
         drain();
         // pass 2 result: closest exact hit over the warp

@@ -64,7 +64,8 @@ struct ObsWarpSmem {
             uint32_t bt[3 * NRAY];            // lidar: bits of the closest hit distance per plane and ray (none: ~0)
             uint16_t bid[3 * NRAY];           // and its box: sorted road slot, or 0x4000 | agent slot; 0x8000: marginal hit
         } l;
-        float stage[32 * 9 + 4];              // row transpose buffer for coalesced stores (+ up to 3 floats of misalignment)
+        float stage[32 * 13 + 4];             // row transpose buffer for coalesced stores (+ up to 3 floats of misalignment);
+                                              // 13 floats per row: the widest row is the fused policy road row
     } u;
     union {                                   // the histogram is only needed after the lidar is written out
         struct {
@@ -117,30 +118,33 @@ __device__ __forceinline__ float rcp_fast(float x) {
 // tfirst = 0, tlast = lidarDistance, "entering t >= tfirst" and "only back faces -> miss" - up to rounding.
 // The reference decides hit / miss in its own float arithmetic (object space, IEEE divisions); this fast form
 // (approximate reciprocals, fused multiply-adds) can disagree with it when the ray grazes a corner, starts on a
-// face or ends at the range limit. So the test is widened by `slack`, a bound on that disagreement - the slab
-// parameters carry a few ulp of the box-frame coordinates, scaled by |1 / direction component|^2 - and every hit
-// or near-miss inside the slack is flagged `marginal`: if such a hit wins its ray, the write-out settles it with
-// the reference's exact clip (and, should that say miss, hands the ray to k_lidar_fix for an exact re-trace).
+// face or ends at the range limit. So each slab's two parameters carry an error bound - a direction component has
+// ~3 eps of absolute error, i.e. 3 eps / |component| relative, which multiplies the parameter (d + |p|) / |component|;
+// the box-frame origin adds ~2 eps of its length - and the test is done on intervals: a pair that is a possible hit
+// but not a certain one is flagged `marginal`; if it wins its ray, k_lidar_fix re-traces the ray with the
+// reference's exact clip. The bounds are per slab: a ray nearly parallel to one axis has huge, imprecise parameters
+// for the other slab, but those do not bind and must not blur the decision (a lumped bound re-traced 1 ray in 370).
 // Nothing exported ever rests on this function's rounding.
 // (px, py): ray origin in the box frame. Explicit fmaf: this translation unit is compiled with --fmad=false.
 __device__ __forceinline__ float ray_box(float px, float py, float cphi, float sphi, float d0, float d1,
                                          float dx, float dy, bool &marginal)
 {
-    // Branch-free slabs. A direction component of exactly 0 gives an infinite reciprocal (and an infinite slack:
+    // Branch-free slabs. A direction component of exactly 0 gives an infinite reciprocal (and an infinite bound:
     // the pair is settled exactly); fminf / fmaxf drop the NaN of 0 * inf (origin exactly on a plane).
     const float lx = fmaf(cphi, dx, sphi * dy), ly = fmaf(cphi, dy, -(sphi * dx));   // direction in box frame
     const float ivx = rcp_fast(lx), ivy = rcp_fast(ly);
     const float x1 = (-d0 - px) * ivx, x2 = (d0 - px) * ivx;
     const float y1 = (-d1 - py) * ivy, y2 = (d1 - py) * ivy;
-    const float tnear = fmaxf(fminf(x1, x2), fminf(y1, y2));
-    const float tfar = fminf(kLidarDistance, fminf(fmaxf(x1, x2), fmaxf(y1, y2)));
-    // |error of a slab parameter| <~ 5 eps * (box-frame coordinates) * (1 / direction component)^2: the direction
-    // component carries ~3 eps of absolute error (the box axis from its quaternion, one fma), i.e. 3 eps /
-    // |component| relative, which multiplies the parameter; the approximate reciprocal adds 1-2 ulp
-    const float iv = fabsf(ivx) + fabsf(ivy);
-    const float slack = 6e-7f * ((fabsf(px) + fabsf(py)) + (d0 + d1)) * iv * iv;
-    marginal = !(tnear >= slack) || !(tnear + slack <= tfar);
-    return (tnear >= -slack && tnear <= tfar + slack) ? fmaxf(tnear, 0.f) : -1.f;
+    const float xmn = fminf(x1, x2), xmx = fmaxf(x1, x2), ymn = fminf(y1, y2), ymx = fmaxf(y1, y2);
+    const float tnear = fmaxf(xmn, ymn);
+    const float apx = fabsf(px), apy = fabsf(py), aivx = fabsf(ivx), aivy = fabsf(ivy), rr = apx + apy;
+    const float ex = 6e-7f * aivx * fmaf(d0 + apx, aivx, rr), ey = 6e-7f * aivy * fmaf(d1 + apy, aivy, rr);
+    const float tn_lo = fmaxf(xmn - ex, ymn - ey), tn_hi = fmaxf(xmn + ex, ymn + ey);
+    const float tf_lo = fminf(kLidarDistance, fminf(xmx - ex, ymx - ey));
+    const float tf_hi = fminf(kLidarDistance, fminf(xmx + ex, ymx + ey));
+    const bool possible = tn_hi >= 0.f && tn_lo <= tf_hi;
+    marginal = !(tn_lo >= 0.f && tn_hi <= tf_lo);
+    return possible ? fmaxf(tnear, 0.f) : -1.f;
 }
 
 // The same clip with the reference's own arithmetic: ray moved into object space (rotate, divide by the
@@ -411,17 +415,24 @@ __device__ __forceinline__ void flush_aligned(const float *stage, float *dst, in
     if (lane < n - t0) dst[t0 + lane] = stage[mis + t0 + lane];
 }
 
-__device__ __forceinline__ void flush_rows(float *stage, float *dst, const float (&row)[9], bool has_row,
-                                           int rank, int m, int lane)
+template <int NF>
+__device__ __forceinline__ void flush_rows_n(float *stage, float *dst, const float (&row)[NF], bool has_row,
+                                             int rank, int m, int lane)
 {
     const int mis = (int)((reinterpret_cast<uintptr_t>(dst) >> 2) & 3u);
     if (has_row) {
 #pragma unroll
-        for (int k = 0; k < 9; k++) stage[mis + rank * 9 + k] = row[k];
+        for (int k = 0; k < NF; k++) stage[mis + rank * NF + k] = row[k];
     }
     __syncwarp();
-    flush_aligned(stage, dst, mis, m * 9, lane);
+    flush_aligned(stage, dst, mis, m * NF, lane);
     __syncwarp();
+}
+
+__device__ __forceinline__ void flush_rows(float *stage, float *dst, const float (&row)[9], bool has_row,
+                                           int rank, int m, int lane)
+{
+    flush_rows_n<9>(stage, dst, row, has_row, rank, m, lane);
 }
 
 } // namespace gd

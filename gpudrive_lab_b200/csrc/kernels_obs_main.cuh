@@ -1,6 +1,7 @@
 // k_obs kernel body (helpers in kernels_obs.cuh).
 #pragma once
 #include "kernels_obs.cuh"
+#include "kernels_policy.cuh"
 
 namespace gd {
 
@@ -10,9 +11,11 @@ namespace gd {
 
 // key_thr: largest float k with sqrtf(k) <= observationRadius, so `key <= key_thr` is exactly the
 // reference's `length() <= radius` (knn.hpp:88, sim.cpp:268-271) without a square root per entity.
+// POL: also write the fused policy observation (second output, `pol`); k_obs<false> carries none of that code.
+template <bool POL>
 __global__ void __launch_bounds__(OBS_BLOCK, GD_OBS_MINB)
 k_obs(const SceneDev *__restrict__ scenes, StateDev st, Exports ex, Params prm, int S, int groups,
-      int write_knn_idx, float key_thr, int only_flagged)
+      int write_knn_idx, float key_thr, int only_flagged, float *__restrict__ pol)
 {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     ObsSmem &sm = *reinterpret_cast<ObsSmem *>(smem_raw);
@@ -21,7 +24,7 @@ k_obs(const SceneDev *__restrict__ scenes, StateDev st, Exports ex, Params prm, 
     const int g = blockIdx.x % groups;
     if (only_flagged && !st.reset_flag[w]) return;      // auto-reset: only the worlds that were just re-bound
     const SceneDev &sc = scenes[st.world_scene[w]];
-    const int A = sc.numAgents;
+    const int A = sc.numAgents, R = sc.numRoads;
     if (g * OBS_WARPS >= A) return;
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -49,6 +52,10 @@ k_obs(const SceneDev *__restrict__ scenes, StateDev st, Exports ex, Params prm, 
         const float4 s0 = sm.a0[a];
         px = s0.x; py = s0.y; qw = s0.z; qz = s0.w; pz = sm.a1[a].x;
     }
+    // optional second output: the flat normalised policy observation GPUDriveTorchEnv.get_obs()
+    // assembles from these rows (kernels_policy.cuh), written from the rows while the warp still holds them
+    // (the address is recomputed where it is used: a pointer held across the kernel costs two of the 64 registers)
+    auto pol_row0 = [&]() { return pol + wa * (size_t)(kPolicyEgo + (S - 1) * kPolicyPartner + kMaxAgentMapObs * kPolicyRoad); };
     const float radius = prm.observationRadius;
     const bool classical = !prm.disableClassicalObs;
     const bool lidar_on = prm.enableLidar != 0;
@@ -70,6 +77,13 @@ k_obs(const SceneDev *__restrict__ scenes, StateDev st, Exports ex, Params prm, 
         ab[4] = make_float2(gc.x, gc.y);
         ab[5] = make_float2(s3.x, s3.y);
         ab[6] = make_float2(s3.z, s1.w);
+        if (POL) {
+            float o[kPolicyEgo];
+            policy_ego_row<true>(s1.y, s3.x, s3.y, gx, gy, st.collided[wa] ? 1.f : 0.f, true, o);
+            float *pe = pol_row0();
+#pragma unroll
+            for (int k = 0; k < kPolicyEgo; k++) pe[k] = o[k];
+        }
     }
 
     // ------------------------------------------------------------ partner observations
@@ -98,6 +112,11 @@ k_obs(const SceneDev *__restrict__ scenes, StateDev st, Exports ex, Params prm, 
                 row[7] = seen ? o1.z : 0.f;
                 row[8] = seen ? o1.w : (exists ? -1.f : -2.f);       // PartnerObservation::zero() / zero_nonexist()
                 flush_rows(wp.u.stage, dst, row, has, lane, m, lane);
+                if (POL) {
+                    float o[kPolicyPartner];
+                    policy_partner_row<true>(row, true, o);
+                    flush_rows_n<kPolicyPartner>(wp.u.stage, pol_row0() + kPolicyEgo + base * kPolicyPartner, o, has, lane, m, lane);
+                }
             } else {
                 // every row of the chunk is zero_nonexist(); chunks start 1152 bytes apart, so the staged image
                 // (and its alignment) is the same for all of them: stage it once
@@ -106,9 +125,16 @@ k_obs(const SceneDev *__restrict__ scenes, StateDev st, Exports ex, Params prm, 
 #pragma unroll
                     for (int k = 0; k < 9; k++) wp.u.stage[mis + lane * 9 + k] = k == 8 ? -2.f : 0.f;
                     __syncwarp();
-                    const_staged = true;
+                    const_staged = !POL;            // (the policy rows below reuse the tile)
                 }
                 flush_aligned(wp.u.stage, dst, mis, m * 9, lane);
+                if (POL) {
+                    __syncwarp();
+                    const float zrow[9] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, -2.f};
+                    float o[kPolicyPartner];
+                    policy_partner_row<true>(zrow, true, o);
+                    flush_rows_n<kPolicyPartner>(wp.u.stage, pol_row0() + kPolicyEgo + base * kPolicyPartner, o, true, lane, m, lane);
+                }
             }
         }
         __syncwarp();
@@ -337,7 +363,6 @@ k_obs(const SceneDev *__restrict__ scenes, StateDev st, Exports ex, Params prm, 
                 // here, and the re-trace as a call, cost every agent up to 25 % more time - 9.2 vs 7.7 ms per launch -
                 // for a path that about one ray in 2 500 takes.)
                 retrace = (id & 0x8000u) != 0;
-                GD_CNT(13, retrace ? 1 : 0);
                 const float2 d = wp.v.g.raydir[i % NRAY];
 #ifdef GD_OBS_FULL_EXACT
                 t = ray_box_exact(px, py, bx, by, bqw, bqz, d0, d1, d.x, d.y);
@@ -603,17 +628,28 @@ k_obs(const SceneDev *__restrict__ scenes, StateDev st, Exports ex, Params prm, 
         row[5] = quat_to_yaw(rw, rz); row[6] = (float)((rc >> 8) & 0xffu); row[7] = rd.z; row[8] = rd.w;
     };
 
+    // one chunk of <= 32 finished rows: the export rows, then (optionally) their policy rows
+    auto pol_road0 = [&]() { return pol_row0() + kPolicyEgo + (S - 1) * kPolicyPartner; };
+    auto emit_chunk = [&](const float (&row)[9], bool acc, int rank, int m, int at) {
+        flush_rows(wp.u.stage, rows + (size_t)at * 9, row, acc, rank, m, lane);
+        if (POL) {
+            float o[kPolicyRoad];
+            policy_road_row<true>(row, true, o);
+            flush_rows_n<kPolicyRoad>(wp.u.stage, pol_road0() + (size_t)at * kPolicyRoad, o, acc, rank, m, lane);
+        }
+    };
 #ifndef GD_OBS_LEAN
     if (first_k_only) {
         // Linear algorithm: the reference emits the first K in-radius entities in road-index order
         // (sim.cpp:261-279), so the order is part of the contract. The selected road indices go into a bit map
-        // (<= 10 000 bits, in the dead group-list / ray buffers); a row's position is the number of selected
-        // indices below its own: one popc after a per-word prefix.
+        // (<= 10 000 bits, in the dead group-list / ray buffers) with a per-word prefix count; the row at output
+        // position p is then the p-th set bit: rows are produced in output order, 32 positions at a time, from the
+        // index-ordered road table, and leave through the same coalesced flush as the k-nearest rows.
         constexpr int BMW = (kMaxRoadEntityCount + 31) / 32;        // 313 words
         static_assert(sizeof(wp.v) >= BMW * 4, "bit map does not fit");
-        static_assert(sizeof(wp.u) >= 320 * 2, "prefix table does not fit");
+        static_assert(sizeof(wp.cpos) >= 320 * 2, "prefix table does not fit");
         uint32_t *bm = reinterpret_cast<uint32_t *>(&wp.v);
-        uint16_t *pre = reinterpret_cast<uint16_t *>(&wp.u);
+        uint16_t *pre = wp.cpos;                                    // (the candidates are dead once the bit map is built)
         __syncwarp();
         for (int i = lane; i < BMW; i += 32) bm[i] = 0u;
         __syncwarp();
@@ -623,42 +659,47 @@ k_obs(const SceneDev *__restrict__ scenes, StateDev st, Exports ex, Params prm, 
         }
         __syncwarp();
         {   // exclusive prefix of the per-word counts: lane owns words [10 * lane, 10 * lane + 10)
-            unsigned sum = 0;
+            unsigned cntw[10]; unsigned sum = 0;
 #pragma unroll
-            for (int k = 0; k < 10; k++) { const int wi = lane * 10 + k; sum += wi < BMW ? __popc(bm[wi]) : 0; }
+            for (int k = 0; k < 10; k++) { const int wi = lane * 10 + k; cntw[k] = wi < BMW ? __popc(bm[wi]) : 0; sum += cntw[k]; }
             unsigned incl = sum;
 #pragma unroll
             for (int o = 1; o < 32; o <<= 1) {
                 const unsigned v = __shfl_up_sync(FULL, incl, o);
                 if (lane >= o) incl += v;
             }
+            emitted = min(K, (int)__shfl_sync(FULL, incl, 31));
+            __syncwarp();                                           // every lane has read the candidates it needed
             unsigned acc = incl - sum;
 #pragma unroll
-            for (int k = 0; k < 10; k++) {
-                const int wi = lane * 10 + k;
-                pre[wi] = (uint16_t)acc;
-                acc += wi < BMW ? __popc(bm[wi]) : 0;
-            }
-            emitted = min(K, (int)__shfl_sync(FULL, incl, 31));
+            for (int k = 0; k < 10; k++) { pre[lane * 10 + k] = (uint16_t)min(acc, 65535u); acc += cntw[k]; }
         }
         __syncwarp();
-        for (int base = 0; base < N; base += 32) {
-            int e; uint32_t rc;
-            const bool acc = candidate(base + lane, e, rc);
-            float row[9];
-            make_row(e, rc, row);
-            const unsigned idx = rc >> 16;
-            const int pos = (int)pre[idx >> 5] + __popc(bm[idx >> 5] & ((1u << (idx & 31u)) - 1u));
-            if (acc && pos < K) {
-#pragma unroll
-                for (int k = 0; k < 9; k++) rows[(size_t)pos * 9 + k] = row[k];
-                if (write_knn_idx) kidx[pos] = (int32_t)idx;
+        for (int base = 0; base < emitted; base += 32) {
+            const int pos = base + lane;
+            const bool acc = pos < emitted;
+            // the word that holds the pos-th set bit: the last one whose prefix count is <= pos
+            int lo = 0, hi = BMW - 1;
+#pragma unroll 1
+            while (lo < hi) {
+                const int mid = (lo + hi + 1) >> 1;
+                if ((int)pre[mid] <= pos) lo = mid; else hi = mid - 1;
             }
+            const unsigned bit = __fns(bm[lo], 0u, (acc ? pos - (int)pre[lo] : 0) + 1);
+            const int r = acc ? min(lo * 32 + (int)(bit & 31u), R - 1) : 0;
+            float row[9];
+            {   // the row of road entity r, from the index-ordered table (same values as make_row over the sorted one)
+                const float4 ra = __ldg(&sc.road_a[r]); const float2 rb = __ldg(&sc.road_b[r]);
+                const float4 rd = __ldg(&sc.road_d[r]);
+                float ox, oy, rw, rz;
+                inv_rotate_xy(qw, qz, __fsub_rn(ra.x, px), __fsub_rn(ra.y, py), ox, oy);
+                inv_mul_quat(qw, qz, ra.z, ra.w, rw, rz);
+                row[0] = ox; row[1] = oy; row[2] = rb.x; row[3] = rb.y; row[4] = rd.x;
+                row[5] = quat_to_yaw(rw, rz); row[6] = (float)(__ldg(&sc.road_c[r]) >> 8); row[7] = rd.z; row[8] = rd.w;
+            }
+            if (acc && write_knn_idx) kidx[pos] = (int32_t)r;
+            emit_chunk(row, acc, lane, min(32, emitted - base), base);
         }
-        // padding rows: MapObservation::zero() (id = -1, mapType = -1), sim.cpp:277-279
-        const int n = (K - emitted) * 9;
-        float *dst = rows + (size_t)emitted * 9;
-        for (int i = lane; i < n; i += 32) dst[i] = (i % 9) >= 7 ? -1.f : 0.f;
     } else
 #endif
     {
@@ -673,18 +714,42 @@ k_obs(const SceneDev *__restrict__ scenes, StateDev st, Exports ex, Params prm, 
             float row[9];
             make_row(e, rc, row);
             if (acc && write_knn_idx) kidx[emitted + rank] = (int32_t)(rc >> 16);
-            flush_rows(wp.u.stage, rows + (size_t)emitted * 9, row, acc, rank, m, lane);
+            emit_chunk(row, acc, rank, m, emitted);
             emitted += m;
         }
-        // padding rows: fillZeros (knn.hpp:19-28 -> all zero, id = 0, mapType = 0). An agent's block of rows is
-        // 16-byte aligned (7 200 bytes per agent): <= 3 scalar zeros up to the boundary, then STG.128
-        const int n = (K - emitted) * 9;
-        float *dst = rows + (size_t)emitted * 9;
-        const int head = min((4 - ((emitted * 9) & 3)) & 3, n);
-        if (lane < head) dst[lane] = 0.f;
+    }
+    {
+        // padding rows: fillZeros (knn.hpp:19-28 -> all zero, id = 0, mapType = 0) for the k-nearest algorithm,
+        // MapObservation::zero() (id = -1, mapType = -1) for the linear one (sim.cpp:277-279). An agent's block of
+        // rows is 16-byte aligned (7 200 bytes per agent): <= 3 scalars up to the boundary, then STG.128
+        const float padv = first_k_only ? -1.f : 0.f;
+        const int n = (K - emitted) * 9, off = emitted * 9;
+        float *dst = rows + (size_t)off;
+        auto padval = [&](int i) { return ((off + i) % 9) >= 7 ? padv : 0.f; };
+        const int head = min((4 - (off & 3)) & 3, n);
+        if (lane < head) dst[lane] = padval(lane);
         float4 *d4 = reinterpret_cast<float4 *>(dst + head);
         const int nq = (n - head) >> 2;              // (K * 9 is a multiple of 4: no tail)
-        for (int i = lane; i < nq; i += 32) d4[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (first_k_only) {
+            for (int i = lane; i < nq; i += 32) {
+                const int j = head + 4 * i;
+                d4[i] = make_float4(padval(j), padval(j + 1), padval(j + 2), padval(j + 3));
+            }
+        } else {
+            for (int i = lane; i < nq; i += 32) d4[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+        if (POL) {
+            // the policy row of a padding row: type 0 either way, everything else the image of zero
+            const float zrow[9] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, padv, padv};
+            float o[kPolicyRoad];
+            policy_road_row<true>(zrow, true, o);
+            float *pd = pol_road0() + (size_t)emitted * kPolicyRoad;
+            const int np = (K - emitted) * kPolicyRoad;
+            for (int i = lane; i < np; i += 32) {
+                const int k = i % kPolicyRoad;
+                pd[i] = k < 2 ? o[0] : (k == 6 ? o[6] : o[2]);      // (o[1] == o[0]; o[2..5] and o[7..12] are equal too)
+            }
+        }
     }
     if (write_knn_idx)
         for (int i = emitted + lane; i < K; i += 32) kidx[i] = -1;

@@ -28,6 +28,49 @@ __device__ __forceinline__ float norm_min_max(float v) {      // normalize_min_m
     return __fsub_rn(__fmul_rn(2.f, tdiv<RCP>(__fsub_rn(v, -1000.f), 2000.f)), 1.f);
 }
 
+// The three row formulas, shared by k_policy_obs below and by the fused second output of k_obs (which uses the
+// CUDA arithmetic, RCP = true: the env that consumes it runs on the device).
+template <bool RCP>
+__device__ __forceinline__ void policy_ego_row(float speed, float length, float width, float gx, float gy,
+                                               float collided, bool normalize, float (&o)[kPolicyEgo])
+{
+    const float len = __fmul_rn(length, 0.7f), wid = __fmul_rn(width, 0.7f);        // madrona_gpudrive.vehicleScale
+    o[0] = normalize ? tdiv<RCP>(speed, 100.f) : speed;
+    o[1] = normalize ? tdiv<RCP>(len, 30.f) : len;
+    o[2] = normalize ? tdiv<RCP>(wid, 15.f) : wid;
+    o[3] = normalize ? norm_min_max<RCP>(gx) : gx;
+    o[4] = normalize ? norm_min_max<RCP>(gy) : gy;
+    o[5] = collided;
+}
+// r: a PartnerObservation row (speed, x, y, heading, length, width, height, type, id)
+template <bool RCP>
+__device__ __forceinline__ void policy_partner_row(const float *r, bool normalize, float (&o)[kPolicyPartner])
+{
+    const float two_pi = 6.283185307179586f;        // float32(2 * np.pi)
+    const float len = __fmul_rn(r[4], 0.7f), wid = __fmul_rn(r[5], 0.7f);
+    o[0] = normalize ? tdiv<RCP>(r[0], 100.f) : r[0];
+    o[1] = normalize ? norm_min_max<RCP>(r[1]) : r[1];
+    o[2] = normalize ? norm_min_max<RCP>(r[2]) : r[2];
+    o[3] = normalize ? tdiv<RCP>(r[3], two_pi) : r[3];
+    o[4] = normalize ? tdiv<RCP>(len, 30.f) : len;
+    o[5] = normalize ? tdiv<RCP>(wid, 15.f) : wid;
+}
+// r: an AgentMapObservation row (x, y, d0, d1, d2, heading, type, id, mapType)
+template <bool RCP>
+__device__ __forceinline__ void policy_road_row(const float *r, bool normalize, float (&o)[kPolicyRoad])
+{
+    const float two_pi = 6.283185307179586f;
+    o[0] = normalize ? norm_min_max<RCP>(r[0]) : r[0];
+    o[1] = normalize ? norm_min_max<RCP>(r[1]) : r[1];
+    o[2] = normalize ? tdiv<RCP>(r[2], 100.f) : r[2];
+    o[3] = normalize ? tdiv<RCP>(r[3], 100.f) : r[3];
+    o[4] = normalize ? tdiv<RCP>(r[4], 100.f) : r[4];
+    o[5] = normalize ? tdiv<RCP>(r[5], two_pi) : r[5];
+    const int ty = (int)r[6];
+#pragma unroll
+    for (int k = 0; k < 7; k++) o[6 + k] = ty == k ? 1.f : 0.f;
+}
+
 // One CTA per agent slot. Inputs are read and the output written with fully coalesced accesses; the row
 // arithmetic happens between two shared-memory images (needs S <= 128: the engine's limit).
 template <bool RCP>
@@ -49,40 +92,23 @@ k_policy_obs(Exports ex, float *__restrict__ out, int S, int normalize)
     for (int i = tid; i < n_po; i += 256) s_po[i] = po[i];
     for (int i = tid; i < n_ro; i += 256) s_ro[i] = ro[i];
     __syncthreads();
-    const float two_pi = 6.283185307179586f;        // float32(2 * np.pi)
-    const float scale = 0.7f;                       // madrona_gpudrive.vehicleScale
     if (tid == 0) {                                 // speed, length, width, goal x, goal y, collided
-        const float len = __fmul_rn(s_in[1], scale), wid = __fmul_rn(s_in[2], scale);
-        s_out[0] = normalize ? tdiv<RCP>(s_in[0], 100.f) : s_in[0];
-        s_out[1] = normalize ? tdiv<RCP>(len, 30.f) : len;
-        s_out[2] = normalize ? tdiv<RCP>(wid, 15.f) : wid;
-        s_out[3] = normalize ? norm_min_max<RCP>(s_in[4]) : s_in[4];
-        s_out[4] = normalize ? norm_min_max<RCP>(s_in[5]) : s_in[5];
-        s_out[5] = s_in[6];
+        float o[kPolicyEgo];
+        policy_ego_row<RCP>(s_in[0], s_in[1], s_in[2], s_in[4], s_in[5], s_in[6], normalize != 0, o);
+#pragma unroll
+        for (int k = 0; k < kPolicyEgo; k++) s_out[k] = o[k];
     }
     if (tid < P) {                                  // speed, x, y, heading, length, width
-        const float *r = s_po + tid * kPartnerObsSize;
-        float *o = s_out + kPolicyEgo + tid * kPolicyPartner;
-        const float len = __fmul_rn(r[4], scale), wid = __fmul_rn(r[5], scale);
-        o[0] = normalize ? tdiv<RCP>(r[0], 100.f) : r[0];
-        o[1] = normalize ? norm_min_max<RCP>(r[1]) : r[1];
-        o[2] = normalize ? norm_min_max<RCP>(r[2]) : r[2];
-        o[3] = normalize ? tdiv<RCP>(r[3], two_pi) : r[3];
-        o[4] = normalize ? tdiv<RCP>(len, 30.f) : len;
-        o[5] = normalize ? tdiv<RCP>(wid, 15.f) : wid;
+        float o[kPolicyPartner];
+        policy_partner_row<RCP>(s_po + tid * kPartnerObsSize, normalize != 0, o);
+#pragma unroll
+        for (int k = 0; k < kPolicyPartner; k++) s_out[kPolicyEgo + tid * kPolicyPartner + k] = o[k];
     }
     if (tid < kMaxAgentMapObs) {                    // x, y, d0, d1, d2, heading, one_hot7(type)
-        const float *r = s_ro + tid * kMapObsSize;
-        float *o = s_out + kPolicyEgo + P * kPolicyPartner + tid * kPolicyRoad;
-        o[0] = normalize ? norm_min_max<RCP>(r[0]) : r[0];
-        o[1] = normalize ? norm_min_max<RCP>(r[1]) : r[1];
-        o[2] = normalize ? tdiv<RCP>(r[2], 100.f) : r[2];
-        o[3] = normalize ? tdiv<RCP>(r[3], 100.f) : r[3];
-        o[4] = normalize ? tdiv<RCP>(r[4], 100.f) : r[4];
-        o[5] = normalize ? tdiv<RCP>(r[5], two_pi) : r[5];
-        const int ty = (int)r[6];
+        float o[kPolicyRoad];
+        policy_road_row<RCP>(s_ro + tid * kMapObsSize, normalize != 0, o);
 #pragma unroll
-        for (int k = 0; k < 7; k++) o[6 + k] = ty == k ? 1.f : 0.f;
+        for (int k = 0; k < kPolicyRoad; k++) s_out[kPolicyEgo + P * kPolicyPartner + tid * kPolicyRoad + k] = o[k];
     }
     __syncthreads();
     float *dst = out + slot * (size_t)width;

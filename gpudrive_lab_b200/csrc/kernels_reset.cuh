@@ -7,6 +7,7 @@
 #pragma once
 #include "device_math.cuh"
 #include "engine.h"
+#include "kernels_policy.cuh"
 
 namespace gd {
 
@@ -15,7 +16,7 @@ constexpr int BIND_SPLIT = 8;
 
 __global__ void __launch_bounds__(256)
 k_bind(const int32_t *__restrict__ worlds, const SceneDev *__restrict__ scenes, StateDev st,
-       Exports ex, int S)
+       Exports ex, int S, float *__restrict__ pol)
 {
     // explicit work list, or (worlds == nullptr, auto-reset) every world whose reset flag is set
     const int w = worlds ? worlds[blockIdx.x] : (int)blockIdx.x;
@@ -108,6 +109,27 @@ k_bind(const int32_t *__restrict__ worlds, const SceneDev *__restrict__ scenes, 
         const long nL = (long)padSlots * 3 * kNumLidarSamples * kLidarRowSize;
         float *lbase = ex.lidar + ((size_t)w * S + A) * 3 * kNumLidarSamples * kLidarRowSize;
         for (long i = tid; i < nL; i += nthr) lbase[i] = 0.f;
+    }
+    if (pol) {
+        // fused policy observation (k_obs writes the live slots every step): the rows of the padding slots are the
+        // image of their constant export rows (self obs zero, partner rows zero(), road-map rows zero() of type 0)
+        const int PW = kPolicyEgo + (S - 1) * kPolicyPartner + kMaxAgentMapObs * kPolicyRoad;
+        const float zrow[9] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, -1.f, -1.f};
+        float oe[kPolicyEgo], op[kPolicyPartner], orow[kPolicyRoad];
+        policy_ego_row<true>(0.f, 0.f, 0.f, 0.f, 0.f, 0.f, true, oe);
+        policy_partner_row<true>(zrow, true, op);
+        policy_road_row<true>(zrow, true, orow);
+        const int road0 = kPolicyEgo + (S - 1) * kPolicyPartner;
+        float *pb = pol + ((size_t)w * S + A) * PW;
+        const long n = (long)(S - A) * PW;
+        for (long i = tid; i < n; i += nthr) {
+            const int k = (int)(i % PW);
+            float v;
+            if (k < kPolicyEgo) v = k < 3 ? oe[0] : (k < 5 ? oe[3] : oe[5]);            // (oe[0..2], oe[3..4] are equal)
+            else if (k < road0) { const int q = (k - kPolicyEgo) % kPolicyPartner; v = (q == 1 || q == 2) ? op[1] : op[0]; }
+            else { const int q = (k - road0) % kPolicyRoad; v = q < 2 ? orow[0] : (q == 6 ? orow[6] : orow[2]); }
+            pb[i] = v;
+        }
     }
     if (tid == 0) {
         ex.shape[w * 2 + 0] = A;

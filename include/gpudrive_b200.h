@@ -202,7 +202,11 @@ int gd_stats(GdHandle h, GdStats *out);
  * GD_OPT_GRAPH (default 1) launches a step as one CUDA graph (the reference's GPU backend does,
  * external/madrona/src/mw/cuda_exec.cpp:1699,1891); GD_OPT_ASYNC_AUX (default 0) lets gd_policy_obs /
  * gd_shaped_reward / gd_expert_actions return without waiting for the device. */
-enum GdOption { GD_OPT_KNN_INDEX = 0, GD_OPT_PROFILE = 1, GD_OPT_GRAPH = 2, GD_OPT_ASYNC_AUX = 3 };
+enum GdOption { GD_OPT_KNN_INDEX = 0, GD_OPT_PROFILE = 1, GD_OPT_GRAPH = 2, GD_OPT_ASYNC_AUX = 3,
+                /* (default 0) the step's observation kernel also writes the gd_policy_obs tensor (normalize = 2,
+                 * torch-CUDA arithmetic) as a second output, from the rows it holds on chip: gd_policy_obs(h, 2, ..)
+                 * then returns it without a launch, and the 11.8 KB per slot it would re-read are never moved */
+                GD_OPT_FUSED_POLICY_OBS = 4 };
 int gd_set_option(GdHandle h, int32_t option, int32_t value);
 /* Accumulated device time (ms) of k_agents / k_obs over the steps taken since GD_OPT_PROFILE was enabled. */
 int gd_kernel_times(GdHandle h, double *agents_ms, double *obs_ms, int64_t *steps);

@@ -157,3 +157,59 @@ def test_device_auto_reset_equals_host_driven_rebind(synth_dir):
     assert int(a.shape_tensor().to_torch()[3, 0]) == n0 - 1
     for n in names:
         assert torch.equal(getattr(a, n)().to_torch(), getattr(b, n)().to_torch()), n
+
+
+@pytest.mark.parametrize("algorithm", [0, 1])      # k-nearest, linear (the env default)
+def test_fused_policy_observation_equals_separate_kernel(synth_dir, algorithm):
+    """GD_OPT_FUSED_POLICY_OBS: the policy observation k_obs writes as a second output, from the
+    rows it holds on chip, equals bit for bit what the separate gd_policy_obs pass computes from the exported
+    tensors (itself pinned against the reference's Python classes) - every slot, padding slots included, across
+    steps, a partial reset, set_maps, deleteAgents and a device-side re-bind."""
+    import os
+    import torch
+    from gpudrive_lab_b200 import synth
+    pool = synth.write_scenarios(os.path.join(synth_dir, "pool_fp"), 4, num_agents=12)
+    big = synth.write_scenarios(synth_dir, 1)          # 64 agents, ~2 000 road entities: rows fill all K = 200
+    scenes = [pool[0], big[0], pool[1]]
+    pd = param_dict(dynamicsModel=2, roadObservationAlgorithm=algorithm, enableLidar=bool(algorithm == 0),
+                    maxNumControlledAgents=64, distanceToGoalThreshold=3.0)
+    f, s = _sim(scenes, pd), _sim(scenes, pd)
+    f.set_option(4, 1)                                 # fused: k_obs<true> + k_bind keep the buffer current
+
+    def check(tag):
+        a = f.policy_observation_tensor(normalize=True, torch_cuda_arithmetic=True).to_torch()
+        b = s.policy_observation_tensor(normalize=True, torch_cuda_arithmetic=True).to_torch()
+        assert a.shape == b.shape == (3, 128, 6 + 127 * 6 + 200 * 13)
+        if not torch.equal(a.view(torch.int32), b.view(torch.int32)):
+            bad = (a.view(torch.int32) != b.view(torch.int32)).nonzero()[:6].tolist()
+            raise AssertionError(f"{tag}: fused policy observation differs at {bad}: "
+                                 f"{[float(a[tuple(i)]) for i in bad]} vs {[float(b[tuple(i)]) for i in bad]}")
+        for n in ("agent_roadmap_tensor", "partner_observations_tensor", "self_observation_tensor"):
+            assert torch.equal(getattr(f, n)().to_torch(), getattr(s, n)().to_torch()), (tag, n)
+
+    check("after enabling")
+    with pytest.raises(RuntimeError):
+        f.policy_observation_tensor(normalize=True, torch_cuda_arithmetic=False)      # the buffer holds the CUDA form
+    launches = f.launch_count()
+    f.policy_observation_tensor(normalize=True, torch_cuda_arithmetic=True)
+    assert f.launch_count() == launches, "the fused read-out must not launch anything"
+    for t in range(14):
+        act = torch.from_numpy(random_actions(t, 3, 128, 2, seed=29))
+        f.action_tensor().to_torch().copy_(act); s.action_tensor().to_torch().copy_(act)
+        f.step(); s.step()
+        check(f"step {t + 1}")
+        if t == 4:
+            f.reset([1]); s.reset([1]); check("partial reset")
+        if t == 7:
+            f.set_maps([pool[2], big[0], pool[3]]); s.set_maps([pool[2], big[0], pool[3]]); check("set_maps")
+        if t == 10:
+            aid = int(f.absolute_self_observation_tensor().to_torch()[0, 2, 13].item())
+            f.deleteAgents({0: [aid]}); s.deleteAgents({0: [aid]}); check("deleteAgents")
+    ida, idb = f.pool_add(pool[0]), s.pool_add(pool[0])
+    f.bind_worlds([1], [ida]); s.bind_worlds([1], [idb])      # a 64-agent world becomes a 12-agent one: 52 new padding slots
+    check("bind_worlds")
+    f.step(); s.step(); check("step after bind_worlds")
+    f.set_option(4, 0)
+    f.step(); s.step()
+    a = f.policy_observation_tensor(normalize=True).to_torch(); b = s.policy_observation_tensor(normalize=True).to_torch()
+    assert torch.equal(a, b)

@@ -17,7 +17,7 @@ sim.step()
 lib.gd_debug_counters(out, 0)
 n = out[0]
 names = ["agents", "groups listed", "groups processed", " with lidar", " with knn", "(box, ray) pairs clipped", "clip-stage calls",
-         "-", "in-radius candidates", "clip rounds", "agents over the candidate cap", "-", "-",
-         "marginal winners (exact clip)", "rays handed to k_lidar_fix"]
+         "-", "in-radius candidates", "clip rounds", "agents over the candidate cap", "k_lidar_fix: road groups reached",
+         "k_lidar_fix: boxes listed for the exact clip", "-", "k_lidar_fix: rays re-traced"]
 for i, nm in enumerate(names):
     print(f"{nm:28s} {out[i]:12d}  per agent {out[i] / max(n, 1):9.2f}")
