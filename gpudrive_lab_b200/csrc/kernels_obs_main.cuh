@@ -282,10 +282,26 @@ k_obs(const SceneDev *__restrict__ scenes, StateDev st, Exports ex, Params prm, 
                 const bool nr = mine && ((desc >> 27) & 1u);
                 unsigned todo = __ballot_sync(FULL, lid || nr);
                 const unsigned lidm = __ballot_sync(FULL, lid), nrm = __ballot_sync(FULL, nr);
+#ifdef GD_OBS_PIPE      // kernel experiment: the next group's position column is loaded while this one is processed
+                uint32_t gdesc_n = 0; float4 ra_n = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (todo) {
+                    gdesc_n = __shfl_sync(FULL, desc, __ffs(todo) - 1);
+                    ra_n = __ldg(&sc.s_a[(g0 + (int)(gdesc_n & 0xfffu)) * 32 + lane]);
+                }
+#endif
                 while (todo) {
                     const int src = __ffs(todo) - 1;
                     todo &= todo - 1;
+#ifdef GD_OBS_PIPE
+                    const uint32_t gdesc = gdesc_n;
+                    const float4 ra = ra_n;
+                    if (todo) {
+                        gdesc_n = __shfl_sync(FULL, desc, __ffs(todo) - 1);
+                        ra_n = __ldg(&sc.s_a[(g0 + (int)(gdesc_n & 0xfffu)) * 32 + lane]);
+                    }
+#else
                     const uint32_t gdesc = __shfl_sync(FULL, desc, src);
+#endif
                     const int gid = g0 + (int)(gdesc & 0xfffu);
                     const bool do_l = (lidm >> src) & 1u;
                     const bool do_n = (nrm >> src) & 1u;
@@ -293,7 +309,9 @@ k_obs(const SceneDev *__restrict__ scenes, StateDev st, Exports ex, Params prm, 
                     GD_CNT(2, 1); GD_CNT(3, do_l ? 1 : 0); GD_CNT(4, do_n ? 1 : 0);
                     // all three columns up front, so their latencies overlap (the kNN-only passes pay two
                     // loads they do not need; they hit L1 / L2)
+#ifndef GD_OBS_PIPE
                     const float4 ra = __ldg(&sc.s_a[e]);
+#endif
                     const uint32_t c = __ldg(&sc.s_c[e]);
                     const float2 rb = __ldg(&sc.s_b[e]);
                     if (do_n) {
