@@ -43,7 +43,10 @@ def k_obs_traffic(config, unique_scenes):
 
 
 class ClockSampler:
-    """nvidia-smi sampled DURING the timed region (B200_PROFILING.md clocks line)."""
+    """nvidia-smi sampled DURING the timed region (B200_PROFILING.md clocks line). It is started ahead of the
+    region (nvidia-smi needs ~0.1 s to produce its first line, an 8-GPU step only 1 ms) and every line is
+    time-stamped on receipt; stop(t0, t1) keeps the samples taken inside [t0, t1], or, if the region was shorter
+    than one sampling period, the ones nearest to it."""
     Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
          "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
@@ -56,7 +59,7 @@ class ClockSampler:
     def start(self):
         try:
             self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
-                                          "-lms", "100", "-i", str(self.gpu)], stdout=subprocess.PIPE, text=True)
+                                          "-lms", "20", "-i", str(self.gpu)], stdout=subprocess.PIPE, text=True)
             self.t = threading.Thread(target=self._read, daemon=True)
             self.t.start()
         except Exception:
@@ -64,16 +67,30 @@ class ClockSampler:
 
     def _read(self):
         for line in self.proc.stdout:
-            self.lines.append(line.strip())
+            self.lines.append((time.time(), line.strip()))
 
-    def stop(self):
+    def wait_ready(self, timeout=2.0):
+        t_end = time.time() + timeout
+        while self.proc and not self.lines and time.time() < t_end:
+            time.sleep(0.01)
+
+    def stop(self, t0=None, t1=None):
         if not self.proc:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        time.sleep(0.15)
+        time.sleep(0.05)
         self.proc.terminate()
+        lines = list(self.lines)
+        window = "timed region"
+        if t0 is not None:
+            inside = [(t, ln) for t, ln in lines if t0 <= t <= t1 + 0.02]
+            if not inside and lines:        # region shorter than a sampling period: the sample(s) nearest to it
+                mid = 0.5 * (t0 + t1)
+                inside = sorted(lines, key=lambda x: abs(x[0] - mid))[:2]
+                window = "nearest to the timed region"
+            lines = inside
         sm, mx, reasons = [], [], set()
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for ln in self.lines:
+        for _, ln in lines:
             f = [x.strip() for x in ln.split(",")]
             if len(f) < 9:
                 continue
@@ -86,7 +103,7 @@ class ClockSampler:
                     reasons.add(n)
         sm.sort()
         return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "samples": len(sm), "reasons": sorted(reasons)}
+                "samples": len(sm), "window": window, "reasons": sorted(reasons)}
 
 
 def measured_peak_gbs():
@@ -306,25 +323,28 @@ def main_engine(args):
             sim.policy_observation_tensor(torch_cuda_arithmetic=True)     # the rollout's read-out, on the device
         step_no[0] += 1
 
+    sampler = ClockSampler(local_rank)
+    sampler.start()                       # ahead of the warm-up: nvidia-smi needs ~0.1 s to produce its first line
     for k in range(args.warmup):
         one_step(k)
     sim.sync()
 
     # ---- timed region: exactly K steps, device time on the engine's stream, max over ranks
-    sampler = ClockSampler(local_rank)
+    sampler.wait_ready()
     sim.set_option(1, 1)
     launches0 = sim.launch_count()
     stats0 = sim.stats()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
-    sampler.start()
+    t_wall0 = time.time()
     ev0.record(stream)
     for k in range(args.steps):
         one_step(args.warmup + k)
     ev1.record(stream)
     sim.sync()
+    t_wall1 = time.time()
     barrier()
-    clocks = sampler.stop()
+    clocks = sampler.stop(t_wall0, t_wall1)
     ms_total = ev0.elapsed_time(ev1)
     launches = sim.launch_count() - launches0 + args.steps     # + the action copy kernel per step
     kt = sim.kernel_times()

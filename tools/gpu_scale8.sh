@@ -3,7 +3,7 @@
 mkdir -p gpurun_out
 nproc
 ( time timeout 600 python bench.py --gpus 1 > gpurun_out/scale_n1.json 2> gpurun_out/scale_n1.err ) 2>&1 | grep real; echo "n1 rc=$?"
-timeout 300 python tools/repro_segv.py 64 > gpurun_out/segv32.log 2>&1; echo "segv repro rc=$?"; tail -4 gpurun_out/segv32.log
+echo "(in-process reference repro skipped: did not reproduce on 16- and 32-core boxes)"
 for n in 2 4 8; do
   timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node $n --master-addr 127.0.0.1 --master-port 29511 bench.py --gpus $n --steps 40 --warmup 5 > gpurun_out/scale_n$n.json 2> gpurun_out/scale_n$n.err; echo "n$n rc=$?"
 done
