@@ -37,6 +37,9 @@ __device__ unsigned long long g_obs_cnt[16];
 #endif
 constexpr int OBS_WARPS = GD_OBS_WARPS;   // agents per CTA
 constexpr int OBS_BLOCK = OBS_WARPS * 32;
+#ifndef GD_OBS_STAGE_W
+#define GD_OBS_STAGE_W 13                 // floats per staged row: the widest row is the fused policy road row
+#endif
 constexpr int OBS_CAND = 512;             // in-radius candidates kept per agent before the slow path
 constexpr int OBS_GCAP = 128;             // group descriptors per pass (4 per lane; larger maps take several passes)
 constexpr int NRAY = kNumLidarSamples;    // 50
@@ -64,7 +67,7 @@ struct ObsWarpSmem {
             uint32_t bt[3 * NRAY];            // lidar: bits of the closest hit distance per plane and ray (none: ~0)
             uint16_t bid[3 * NRAY];           // and its box: sorted road slot, or 0x4000 | agent slot; 0x8000: marginal hit
         } l;
-        float stage[32 * 13 + 4];             // row transpose buffer for coalesced stores (+ up to 3 floats of misalignment);
+        float stage[32 * GD_OBS_STAGE_W + 4];             // row transpose buffer for coalesced stores (+ up to 3 floats of misalignment);
                                               // 13 floats per row: the widest row is the fused policy road row
     } u;
     union {                                   // the histogram is only needed after the lidar is written out
