@@ -138,6 +138,13 @@ void Engine::allocExports() {
     st_.pos = devAlloc<float4>(owned_, WS);
     st_.rv = devAlloc<float4>(owned_, WS);
     st_.yaw = devAlloc<float>(owned_, WS);
+    st_.cost = devAlloc<uint32_t>(owned_, WS);
+    st_.order = devAlloc<uint8_t>(owned_, WS);
+    {
+        std::vector<uint8_t> ident(WS);
+        for (size_t i = 0; i < WS; i++) ident[i] = (uint8_t)(i % (size_t)S_);
+        GD_CUDA(cudaMemcpy(st_.order, ident.data(), WS, cudaMemcpyHostToDevice));
+    }
     st_.collided = devAlloc<int32_t>(owned_, WS);
     st_.world_scene = devAlloc<int32_t>(owned_, W_);
     st_.reset_flag = devAlloc<int32_t>(owned_, W_);

@@ -85,6 +85,9 @@ struct StateDev {
     int32_t *collided;    // [W,S] CollisionDetectionEvent.hasCollided
     int32_t *world_scene; // [W]
     int32_t *reset_flag;  // [W]
+    uint32_t *cost;       // [W,S] cycles k_obs spent on the agent in its last launch
+    uint8_t *order;       // [W,S] the world's agents by decreasing cost (k_agents): k_obs takes agents in this order, so
+                          //       the eight warps of a CTA carry agents of similar cost (results do not depend on it)
     uint32_t *retrace;         // [1 + kRetraceCap] lidar rays k_obs hands to k_lidar_fix: count, then slot * 150 + ray
     unsigned long long *stats; // [16] episode statistics accumulators (StatSlot), written by k_agents
 };

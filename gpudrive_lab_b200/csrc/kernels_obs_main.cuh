@@ -41,8 +41,14 @@ k_obs(const SceneDev *__restrict__ scenes, StateDev st, Exports ex, Params prm, 
     }
     __syncthreads();
 
-    const int a = g * OBS_WARPS + warp;
-    if (a >= A) return;                   // no block-wide barrier below this point
+    const int turn = g * OBS_WARPS + warp;
+    if (turn >= A) return;                // no block-wide barrier below this point
+#ifndef GD_OBS_NO_COSTSORT
+    const unsigned clk0 = (unsigned)clock();
+    const int a = st.order[(size_t)w * S + turn];      // agents in order of decreasing cost (k_agents)
+#else
+    const int a = turn;
+#endif
     const bool active = true;
     ObsWarpSmem &wp = sm.wp[warp];
     const size_t wa = (size_t)w * S + (active ? a : 0);
@@ -400,7 +406,12 @@ k_obs(const SceneDev *__restrict__ scenes, StateDev st, Exports ex, Params prm, 
     }
 
     // ------------------------------------------------------------ road-map rows
-    if (!classical) return;
+    if (!classical) {
+#ifndef GD_OBS_NO_COSTSORT
+        if (lane == 0) st.cost[wa] = (unsigned)clock() - clk0;
+#endif
+        return;
+    }
     const int K = kMaxAgentMapObs;
     float *rows = ex.agent_roadmap + wa * K * kMapObsSize;
     int32_t *kidx = ex.knn_idx + wa * K;
@@ -771,6 +782,9 @@ k_obs(const SceneDev *__restrict__ scenes, StateDev st, Exports ex, Params prm, 
     }
     if (write_knn_idx)
         for (int i = emitted + lane; i < K; i += 32) kidx[i] = -1;
+#ifndef GD_OBS_NO_COSTSORT
+    if (lane == 0) st.cost[wa] = (unsigned)clock() - clk0;
+#endif
 }
 
 } // namespace gd

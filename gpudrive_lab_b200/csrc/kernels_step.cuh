@@ -58,6 +58,7 @@ k_agents(const SceneDev *__restrict__ scenes, StateDev st, Exports ex, Params pr
     AgentBox *box = reinterpret_cast<AgentBox *>(smem_raw);
     // episode statistics of this world's step (gd_stats): 0 -> 1 transitions of the Info / Done flags
     __shared__ unsigned s_cnt[ST_NUM];
+    __shared__ unsigned s_cost[128];                   // (max_agents <= 128, engine.cu)
     if (threadIdx.x < ST_NUM) s_cnt[threadIdx.x] = 0;
     if (blockIdx.x == 0 && threadIdx.x == 0) st.retrace[0] = 0;     // k_obs -> k_lidar_fix hand-off list of this step
 
@@ -72,6 +73,7 @@ k_agents(const SceneDev *__restrict__ scenes, StateDev st, Exports ex, Params pr
     // ------------------------------------------------------------------ phase A: movement
     for (int a = tid; a < A; a += BLOCK) {
         const size_t wa = (size_t)w * S + a;
+        s_cost[a] = st.cost[wa];
         float4 p = st.pos[wa];
         float4 rv = st.rv[wa];
         int collided = st.collided[wa];
@@ -307,6 +309,16 @@ k_agents(const SceneDev *__restrict__ scenes, StateDev st, Exports ex, Params pr
         if (decrement && done == 1 && !(box[a].flags & AB_DONE0)) atomicAdd(&s_cnt[ST_DONES], 1u);
         ex.done[wa] = done;
     }
+#ifndef GD_OBS_NO_COSTSORT
+    // k_obs work order: the world's agents by decreasing cost of their last observation pass (ties: lower slot), so
+    // that the warps of one k_obs CTA finish together; any permutation gives the same results
+    for (int a = tid; a < A; a += BLOCK) {
+        const unsigned c = s_cost[a];
+        int r = 0;
+        for (int j = 0; j < A; j++) { const unsigned cj = s_cost[j]; r += (cj > c || (cj == c && j < a)) ? 1 : 0; }
+        st.order[(size_t)w * S + r] = (uint8_t)a;
+    }
+#endif
     if (decrement) {
         __syncthreads();
         if (tid < ST_NUM && s_cnt[tid]) atomicAdd(&st.stats[tid], (unsigned long long)s_cnt[tid]);
