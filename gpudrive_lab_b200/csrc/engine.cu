@@ -154,8 +154,20 @@ void Engine::allocExports() {
     d_act_stage_ = devAlloc<float>(owned_, (size_t)W_ * S_ * kActionSize);
 }
 
-void *Engine::arenaAlloc(size_t bytes) {
+void *Engine::arenaAlloc(size_t bytes, size_t *block_bytes) {
     bytes = (bytes + 255) & ~size_t(255);
+    // a block an evicted scene left behind, if one fits without wasting more than half of it (best fit)
+    int best = -1;
+    for (int i = 0; i < (int)arena_free_.size(); i++)
+        if (arena_free_[i].second >= bytes && arena_free_[i].second <= 2 * bytes &&
+            (best < 0 || arena_free_[i].second < arena_free_[best].second)) best = i;
+    if (best >= 0) {
+        void *out = arena_free_[best].first;
+        *block_bytes = arena_free_[best].second;
+        arena_free_.erase(arena_free_.begin() + best);
+        return out;
+    }
+    *block_bytes = bytes;
     if (arena_slabs_.empty() || arena_off_ + bytes > arena_cap_) {
         size_t cap = std::max(ARENA_SLAB, bytes);
         void *p = nullptr;
@@ -386,7 +398,8 @@ int Engine::uploadScene(const SceneData &s, const std::string &key) {
         ac[a] = make_float4(s.goal[a * 2], s.goal[a * 2 + 1], (float)s.response[a], (float)s.controlled[a]);
         me[a] = make_int4(s.meta[a * 4], s.meta[a * 4 + 1], s.meta[a * 4 + 2], s.meta[a * 4 + 3]);
     }
-    char *base = static_cast<char *>(arenaAlloc(blob.size()));
+    size_t block_bytes = 0;
+    char *base = static_cast<char *>(arenaAlloc(blob.size(), &block_bytes));
     GD_CUDA(cudaMemcpy(base, blob.data(), blob.size(), cudaMemcpyHostToDevice));
     dev.road_a = reinterpret_cast<const float4 *>(base + o_ra);
     dev.road_b = reinterpret_cast<const float2 *>(base + o_rb);
@@ -414,12 +427,39 @@ int Engine::uploadScene(const SceneData &s, const std::string &key) {
 
     SceneHost h;
     h.key = key; h.dev = dev; h.numAgents = A; h.numRoads = R; h.numControlled = s.numControlled;
-    scenes_.push_back(h);
-    scene_index_[key] = (int)scenes_.size() - 1;
+    h.block = base; h.block_bytes = block_bytes; h.last_use = bind_generation_;
+    int id;
+    if (!free_ids_.empty()) { id = free_ids_.back(); free_ids_.pop_back(); scenes_[id] = h; }
+    else { scenes_.push_back(h); id = (int)scenes_.size() - 1; }
+    scene_index_[key] = id;
     max_roads_ = std::max(max_roads_, R);
     max_scene_agents_ = std::max(max_scene_agents_, A);
     scene_table_dirty_ = true;
-    return (int)scenes_.size() - 1;
+    return id;
+}
+
+// Bound the scenario cache (an env that resamples with set_maps over a large dataset would otherwise grow it by
+// ~0.4 MB per scenario for ever): scenes no world is bound to and whose id no caller holds are kept up to a budget
+// of max(W, 64), oldest use first out; their arena blocks and ids are reused by later uploads. Called with the
+// stream idle (set_maps / deleteAgents are synchronous calls), so no kernel in flight reads an evicted table.
+void Engine::evictUnusedScenes() {
+    std::vector<char> bound(scenes_.size(), 0);
+    for (int w = 0; w < W_; w++) bound[world_scene_[w]] = 1;
+    std::vector<int> idle;
+    for (int i = 0; i < (int)scenes_.size(); i++)
+        if (scenes_[i].live && !scenes_[i].pinned && !bound[i]) idle.push_back(i);
+    const size_t keep = (size_t)std::max(W_, 64);
+    if (idle.size() <= keep) return;
+    std::sort(idle.begin(), idle.end(), [&](int a, int b) { return scenes_[a].last_use < scenes_[b].last_use; });
+    for (size_t k = 0; k + keep < idle.size(); k++) {
+        SceneHost &h = scenes_[idle[k]];
+        scene_index_.erase(h.key);
+        arena_free_.emplace_back(h.block, h.block_bytes);
+        h.live = false; h.block = nullptr; h.block_bytes = 0; h.key.clear();
+        h.dev = SceneDev{};
+        free_ids_.push_back(idle[k]);
+    }
+    scene_table_dirty_ = true;
 }
 
 int Engine::sceneFor(const std::string &path, const std::vector<int32_t> &deleted) {
@@ -429,7 +469,7 @@ int Engine::sceneFor(const std::string &path, const std::vector<int32_t> &delete
         for (int32_t d : deleted) key += ":" + std::to_string(d);
     }
     auto it = scene_index_.find(key);
-    if (it != scene_index_.end()) return it->second;
+    if (it != scene_index_.end()) { scenes_[it->second].last_use = bind_generation_; return it->second; }
     std::shared_ptr<ParsedMap> pm;
     auto pit = parsed_cache_.find(path);
     if (pit != parsed_cache_.end()) pm = pit->second;
@@ -623,10 +663,13 @@ void Engine::setMaps(const std::vector<std::string> &scenes) {
     GD_CUDA(cudaSetDevice(gpu_));
     host_binding_stale_ = false;
     scene_paths_ = scenes;
+    GD_CUDA(cudaStreamSynchronize(stream_));         // blocks of evicted scenes are reused below: nothing may still read them
+    bind_generation_++;
     for (int w = 0; w < W_; w++) {
         deleted_[w].clear();                         // src/mgr.cpp:643-646
         world_scene_[w] = sceneFor(scenes[w], deleted_[w]);
     }
+    evictUnusedScenes();
     GD_CUDA(cudaMemset(ex_.deleted, 0xff, (size_t)W_ * S_ * sizeof(int32_t)));
     GD_CUDA(cudaMemcpy(st_.world_scene, world_scene_.data(), W_ * sizeof(int32_t), cudaMemcpyHostToDevice));
     std::vector<int32_t> all(W_);
@@ -663,7 +706,10 @@ void Engine::deleteAgents(int world, const int32_t *ids, int n) {
 
 int Engine::poolAdd(const std::string &path) {
     GD_CUDA(cudaSetDevice(gpu_));
-    return sceneFor(path, {});
+    GD_CUDA(cudaStreamSynchronize(stream_));         // (an upload may reuse the block of an evicted scene)
+    const int id = sceneFor(path, {});
+    scenes_[id].pinned = true;                       // the caller holds the id
+    return id;
 }
 
 void Engine::bindWorlds(const int32_t *worlds, const int32_t *scene_ids, int n) {
@@ -672,11 +718,13 @@ void Engine::bindWorlds(const int32_t *worlds, const int32_t *scene_ids, int n) 
     std::vector<int32_t> list;
     for (int i = 0; i < n; i++) {
         if (worlds[i] < 0 || worlds[i] >= W_) throw std::runtime_error("bind: world index out of range");
-        if (scene_ids[i] < 0 || scene_ids[i] >= (int)scenes_.size()) throw std::runtime_error("bind: scene id out of range");
+        if (scene_ids[i] < 0 || scene_ids[i] >= (int)scenes_.size() || !scenes_[scene_ids[i]].live)
+            throw std::runtime_error("bind: scene id out of range");
     }
     if (n > W_) throw std::runtime_error("bind: more entries than worlds");
     for (int i = 0; i < n; i++) {
         world_scene_[worlds[i]] = scene_ids[i];
+        scenes_[scene_ids[i]].pinned = true;
         scene_paths_[worlds[i]] = scenes_[scene_ids[i]].key;
         list.push_back(worlds[i]);
     }
@@ -695,7 +743,9 @@ void Engine::autoResetPool(const int32_t *scene_ids, int n) {
     GD_CUDA(cudaSetDevice(gpu_));
     if (n <= 0) throw std::runtime_error("auto_reset_pool: empty pool");
     for (int i = 0; i < n; i++)
-        if (scene_ids[i] < 0 || scene_ids[i] >= (int)scenes_.size()) throw std::runtime_error("auto_reset_pool: scene id out of range");
+        if (scene_ids[i] < 0 || scene_ids[i] >= (int)scenes_.size() || !scenes_[scene_ids[i]].live)
+            throw std::runtime_error("auto_reset_pool: scene id out of range");
+    for (int i = 0; i < n; i++) scenes_[scene_ids[i]].pinned = true;
     GD_CUDA(cudaStreamSynchronize(stream_));
     if (d_pool_ids_) GD_CUDA(cudaFree(d_pool_ids_));
     GD_CUDA(cudaMalloc(&d_pool_ids_, sizeof(int32_t) * (size_t)n));

@@ -167,10 +167,16 @@ private:
         std::string key;
         SceneDev dev;
         int32_t numAgents, numRoads, numControlled;
+        void *block = nullptr;       // arena block holding the scene's tables
+        size_t block_bytes = 0;
+        bool live = true;            // false: evicted, the id waits in free_ids_ for the next upload
+        bool pinned = false;         // the caller holds the id (gd_pool_add, gd_bind_worlds, gd_auto_reset_pool): never evicted
+        uint64_t last_use = 0;       // set_maps / deleteAgents generation that last bound a world to it
     };
     int sceneFor(const std::string &path, const std::vector<int32_t> &deleted);
     int uploadScene(const SceneData &s, const std::string &key);
-    void *arenaAlloc(size_t bytes);
+    void *arenaAlloc(size_t bytes, size_t *block_bytes);
+    void evictUnusedScenes();
     void syncSceneTable();
     void launchBindReset(const std::vector<int32_t> &worlds, bool rebind, bool scene_ids_uploaded = false);
     void launchRest(bool decrement, bool only_flagged = false);
@@ -191,6 +197,9 @@ private:
     bool scene_table_dirty_ = true;
     std::vector<void *> arena_slabs_;
     size_t arena_off_ = 0, arena_cap_ = 0;
+    std::vector<std::pair<void *, size_t>> arena_free_;   // blocks of evicted scenes, reused by later uploads
+    std::vector<int> free_ids_;                           // scene ids of evicted scenes
+    uint64_t bind_generation_ = 0;
     int max_roads_ = 0;        // over the pool
     int max_scene_agents_ = 0; // over the pool: k_obs launches CTAs for these slots only
     Exports ex_{};

@@ -82,6 +82,45 @@ def test_device_scenario_pool_rebind(tmp_path):
     assert int(sim.steps_remaining_tensor().to_torch()[0, 0, 0]) == 91 - 3      # world 0 untouched
 
 
+def test_scene_cache_is_bounded_under_set_maps_churn(tmp_path):
+    """An env that resamples with set_maps over a large dataset (swap_data_batch) must not grow the device scenario
+    cache for ever: scenes no world is bound to are evicted beyond max(W, 64) and their ids / arena blocks reused,
+    while ids the caller holds (pool_add) stay valid, and a scene that comes back after eviction is rebuilt
+    identically."""
+    import torch
+    from gpudrive_lab_b200 import synth
+    paths = []
+    for i in range(0, 150, 15):       # (batches below write_scenarios' fork-pool threshold: this process has threads)
+        paths += synth.write_scenarios(str(tmp_path / "many"), 15, start_index=i, num_agents=4, extent=80.0, spacing=2.0)
+    pd = param_dict(dynamicsModel=2, maxNumControlledAgents=4)
+    sim = _sim(paths[:2], pd, S=8)
+    pinned = sim.pool_add(paths[2])                    # id 2, held by the caller across the churn
+    assert pinned == 2
+    for i in range(4, 150, 2):                         # 73 calls, 146 further distinct scenes
+        sim.set_maps(paths[i:i + 2])
+        sim.step()
+    fresh_id = sim.pool_add(paths[3])                  # never seen before: takes a recycled id, not id >= 149
+    assert fresh_id < 80, fresh_id
+    names = ("shape_tensor", "map_observation_tensor", "expert_trajectory_tensor", "self_observation_tensor",
+             "agent_roadmap_tensor", "partner_observations_tensor", "absolute_self_observation_tensor", "done_tensor")
+    # scenes evicted long ago come back bit-identical to a fresh engine; the held id still binds to its scene
+    sim.set_maps(paths[:2])
+    ref = _sim(paths[:2], pd, S=8)
+    for name in names:
+        assert torch.equal(getattr(sim, name)().to_torch(), getattr(ref, name)().to_torch()), name
+    sim.bind_worlds([0], [pinned])
+    ref2 = _sim([paths[2], paths[1]], pd, S=8)
+    for name in names:
+        assert torch.equal(getattr(sim, name)().to_torch(), getattr(ref2, name)().to_torch()), name
+    # and the most recent scenes were still cached (binding them again needs no upload: same behaviour either way)
+    sim.set_maps(paths[148:150])
+    ref3 = _sim(paths[148:150], pd, S=8)
+    for _ in range(3):
+        sim.step(); ref3.step()
+    for name in names:
+        assert torch.equal(getattr(sim, name)().to_torch(), getattr(ref3, name)().to_torch()), name
+
+
 def test_errors_are_reported_not_fatal(tmp_path):
     scenes = unpack(["synth_a"], tmp_path)
     sim = _sim(scenes, param_dict())
