@@ -360,18 +360,8 @@ __device__ __forceinline__ void lidar_expand(ObsWarpSmem &wp, int lane, int lo, 
         const int j = base + lane;
         const unsigned rel = (unsigned)(excl - base);
         const unsigned starts = __reduce_or_sync(FULL, (n > 0 && rel < 32u) ? (1u << rel) : 0u);
-#ifdef GD_OBS_BSEARCH      // kernel experiments: the round-1 owner search, five dependent shuffles
-        int s = 0;
-#pragma unroll
-        for (int step = 16; step > 0; step >>= 1) {
-            const int v = __shfl_sync(FULL, incl, s + step - 1);
-            if (v <= j) s += step;
-        }
-        (void)starts;
-#else
         const int s = wp.own[r0 + __popc(starts & (FULL >> (31 - lane))) - 1];      // (round 0 starts at position 0)
         r0 += __popc(starts);
-#endif
         const float spx = __shfl_sync(FULL, opx, s), spy = __shfl_sync(FULL, opy, s);
         const float sc_ = __shfl_sync(FULL, cphi, s), ss_ = __shfl_sync(FULL, sphi, s);
         const float sd0 = __shfl_sync(FULL, d0, s), sd1 = __shfl_sync(FULL, d1, s);

@@ -167,11 +167,7 @@ k_obs(const SceneDev *__restrict__ scenes, StateDev st, Exports ex, Params prm, 
             // is 1 ulp off moves the depth of a ray that runs nearly parallel to a long thin box by far more than
             // 1e-5 (CUDA's sincosf, <= 2 ulp away, cost 7 of 2.4 M rays their parity on the benchmarked scenes).
             float x, y;
-#ifdef GD_OBS_FAST_DIRS
-            sincosf(theta, &y, &x);
-#else
             sincos_hp(theta, y, x);
-#endif
             const float dx = __fadd_rn(__fmul_rn(x, rgx), __fmul_rn(y, fwx));
             const float dy = __fadd_rn(__fmul_rn(x, rgy), __fmul_rn(y, fwy));
             const float inv = __fdiv_rn(1.f, __fsqrt_rn(__fadd_rn(len2_xy(dx, dy), 0.f)));
@@ -279,35 +275,17 @@ k_obs(const SceneDev *__restrict__ scenes, StateDev st, Exports ex, Params prm, 
                 const int li = base + lane;
                 const uint32_t desc = li < nlist ? wp.v.g.glist[li] : 0u;
                 const bool mine = li < nlist && (int)((desc >> 12) & 7u) == band;
-#ifndef GD_OBS_NO_CHUNK_SKIP
                 if (!__any_sync(FULL, mine)) continue;       // no group of this band in this chunk of the list
-#endif
                 const int pmg = (int)(desc >> 28);
                 const bool lid = mine && pmg != 0 &&
                     (ray_bits((desc >> 15) & 63u, (desc >> 21) & 63u) & open_for(open, pmg)) != 0ull;
                 const bool nr = mine && ((desc >> 27) & 1u);
                 unsigned todo = __ballot_sync(FULL, lid || nr);
                 const unsigned lidm = __ballot_sync(FULL, lid), nrm = __ballot_sync(FULL, nr);
-#ifdef GD_OBS_PIPE      // kernel experiment: the next group's position column is loaded while this one is processed
-                uint32_t gdesc_n = 0; float4 ra_n = make_float4(0.f, 0.f, 0.f, 0.f);
-                if (todo) {
-                    gdesc_n = __shfl_sync(FULL, desc, __ffs(todo) - 1);
-                    ra_n = __ldg(&sc.s_a[(g0 + (int)(gdesc_n & 0xfffu)) * 32 + lane]);
-                }
-#endif
                 while (todo) {
                     const int src = __ffs(todo) - 1;
                     todo &= todo - 1;
-#ifdef GD_OBS_PIPE
-                    const uint32_t gdesc = gdesc_n;
-                    const float4 ra = ra_n;
-                    if (todo) {
-                        gdesc_n = __shfl_sync(FULL, desc, __ffs(todo) - 1);
-                        ra_n = __ldg(&sc.s_a[(g0 + (int)(gdesc_n & 0xfffu)) * 32 + lane]);
-                    }
-#else
                     const uint32_t gdesc = __shfl_sync(FULL, desc, src);
-#endif
                     const int gid = g0 + (int)(gdesc & 0xfffu);
                     const bool do_l = (lidm >> src) & 1u;
                     const bool do_n = (nrm >> src) & 1u;
@@ -315,9 +293,7 @@ k_obs(const SceneDev *__restrict__ scenes, StateDev st, Exports ex, Params prm, 
                     GD_CNT(2, 1); GD_CNT(3, do_l ? 1 : 0); GD_CNT(4, do_n ? 1 : 0);
                     // all three columns up front, so their latencies overlap (the kNN-only passes pay two
                     // loads they do not need; they hit L1 / L2)
-#ifndef GD_OBS_PIPE
                     const float4 ra = __ldg(&sc.s_a[e]);
-#endif
                     const uint32_t c = __ldg(&sc.s_c[e]);
                     const float2 rb = __ldg(&sc.s_b[e]);
                     if (do_n) {
@@ -388,11 +364,7 @@ k_obs(const SceneDev *__restrict__ scenes, StateDev st, Exports ex, Params prm, 
                 // for a path that about one ray in 2 500 takes.)
                 retrace = (id & 0x8000u) != 0;
                 const float2 d = wp.v.g.raydir[i % NRAY];
-#ifdef GD_OBS_FULL_EXACT
-                t = ray_box_exact(px, py, bx, by, bqw, bqz, d0, d1, d.x, d.y);
-#else
                 t = ray_box_exact_depth(px, py, bx, by, bqw, bqz, d0, d1, d.x, d.y);
-#endif
                 const float2 xy = wp.v.g.rayxy[i % NRAY];
                 v = make_float4(t, (float)type, __fmul_rn(t, xy.x), __fmul_rn(t, xy.y));
             }
@@ -465,7 +437,6 @@ k_obs(const SceneDev *__restrict__ scenes, StateDev st, Exports ex, Params prm, 
         inbin = __shfl_sync(FULL, inbin, src);
     };
 
-#ifndef GD_OBS_LEAN
     if (cnt > OBS_CAND) {
         // Dense map: more in-radius entities than the candidate buffer holds (a 10 000-entity scene has ~900 within
         // 50 m). Two more sweeps over the near groups only: a histogram of the quantised keys finds the bin of the
@@ -513,12 +484,7 @@ k_obs(const SceneDev *__restrict__ scenes, StateDev st, Exports ex, Params prm, 
             __syncwarp();
         }
     }
-#endif
-#ifdef GD_OBS_LEAN
-    const bool overflow = false;
-#else
     const bool overflow = cnt > OBS_CAND;
-#endif
     const int C = min(cnt, OBS_CAND);
     const bool take_all = cnt <= K;
     const int N = overflow ? RS : C;
@@ -562,7 +528,6 @@ k_obs(const SceneDev *__restrict__ scenes, StateDev st, Exports ex, Params prm, 
             __syncwarp();
         }
     }
-#ifndef GD_OBS_LEAN
     if (!selected) {
         // general path (candidate overflow, or many equal keys): exact radix select (4 x 8 bits, MSB first)
         // of the K-th smallest key among in-radius entities
@@ -633,7 +598,6 @@ k_obs(const SceneDev *__restrict__ scenes, StateDev st, Exports ex, Params prm, 
         }
     }
 
-#endif
     // One chunk of 32 candidates: is entry i selected, and which sorted slot / road word does it carry?
     auto candidate = [&](int i, int &e, uint32_t &rc) -> bool {
         bool acc = false; unsigned kb = 0;
@@ -667,7 +631,6 @@ k_obs(const SceneDev *__restrict__ scenes, StateDev st, Exports ex, Params prm, 
             flush_rows_n<kPolicyRoad>(wp.u.stage, pol_road0() + (size_t)at * kPolicyRoad, o, acc, rank, m, lane);
         }
     };
-#ifndef GD_OBS_LEAN
     if (first_k_only) {
         // Linear algorithm: the reference emits the first K in-radius entities in road-index order
         // (sim.cpp:261-279), so the order is part of the contract. The selected road indices go into a bit map
@@ -730,7 +693,6 @@ k_obs(const SceneDev *__restrict__ scenes, StateDev st, Exports ex, Params prm, 
             emit_chunk(row, acc, lane, min(32, emitted - base), base);
         }
     } else
-#endif
     {
         // k-nearest: the reference leaves the rows in heap order; here by distance band, then by sorted slot
         for (int base = 0; base < N && emitted < K; base += 32) {
