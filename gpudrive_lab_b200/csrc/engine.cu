@@ -25,7 +25,10 @@ namespace gd {
                                      " at " #expr);                                           \
     } while (0)
 
-static constexpr int AGENTS_BLOCK = 256;
+#ifndef GD_AGENTS_BLOCK
+#define GD_AGENTS_BLOCK 256
+#endif
+static constexpr int AGENTS_BLOCK = GD_AGENTS_BLOCK;
 static constexpr size_t ARENA_SLAB = 256ull << 20;
 
 template <typename T>

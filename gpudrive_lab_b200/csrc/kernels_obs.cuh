@@ -5,20 +5,27 @@
 //   lidarSystem + BVH::traceRay + traceRayIntoConvexPolyhedron  src/sim.cpp:394-460,
 //                                   external/madrona/src/physics/broadphase.cpp:656-888
 //
-// Road entities arrive spatially sorted in groups of 32 with a bounding circle per group (SceneDev::grp),
-// a one-level stand-in for the reference's BVH that fits a warp: one lane tests one group, and a group
-// that survives is processed by all 32 lanes at once.
-//   k-nearest: groups whose circle reaches the observation radius -> exact squared-distance keys ->
-//     in-radius candidates -> exact radix select of the K smallest (key, road index). The keys use the
-//     reference's operation order, so the selected SET is bit-exact.
-//   lidar: groups are visited in bands of increasing distance. Before each band the rays that are still
-//     "open" (no hit closer than the band) are gathered into one bit mask per plane; a group, and then a
-//     box, is skipped with one AND if the rays its angular range covers are all closed. The warp expands the
-//     surviving (box, ray range) pairs of a pass into (box, ray) pairs, 32 per round, one per lane (prefix sum
-//     + owner search over shuffles: no queue), so 32 lanes clip rays in lock step; the closest hit per ray is
-//     kept with a native 32-bit shared atomicMin on the bits of t, the box id written by the lane that holds
-//     the minimum. At write-out the deciding face of each winner is evaluated with the reference's exact
-//     object-space arithmetic, so exported depths carry its rounding.
+// Road entities arrive sorted by (z-class, Morton code) in groups of 32 with two bounds per group (SceneDev::grp):
+// an oriented rectangle along the principal axis of the member boxes, used for every distance decision, and the
+// circle around the same centre, used for the angular range. A one-level stand-in for the reference's BVH that
+// fits a warp: one lane tests one group, and a group that survives is processed by all 32 lanes at once.
+//   k-nearest: groups whose rectangle reaches the observation radius -> exact squared-distance keys in the
+//     reference's operation order -> in-radius candidates -> histogram selection of the K smallest (key, road
+//     index); dense maps refine over the near groups first, an exact radix select is the last resort. The selected
+//     SET is bit-exact. The linear algorithm uses the road index as the key and emits rows in index order.
+//   lidar: ray directions with glibc's own sincosf (gdtrig::sincosf_glibc). Groups are visited in bands of
+//     increasing distance. Before each band the rays that are still "open" (no hit closer than the band) are
+//     gathered into one bit mask per plane; a group, and then a box, is skipped with one AND if the rays its
+//     angular range covers are all closed. The warp expands the surviving (box, ray range) pairs of a pass into
+//     (box, ray) pairs, 32 per round, one per lane (prefix sum + a per-warp owner table: no queue), so 32 lanes
+//     clip rays in lock step. The clip (ray_box) is a box-frame slab test on intervals: every slab parameter
+//     carries its rounding bound, a hit is "certain" or "marginal". The closest hit per ray is kept with a native
+//     32-bit shared atomicMin on the bits of t, the box id (+ the marginal flag) written by the lane that holds
+//     the minimum. At write-out the deciding face of a certain winner is evaluated with the reference's exact
+//     object-space arithmetic, so exported depths carry its rounding; a ray whose winner is marginal is handed
+//     to k_lidar_fix (kernels_lidar_fix.cuh), which re-traces it exactly.
+//   rows leave through a per-warp staging tile as 16-byte vector stores (flush_aligned); k_obs<true> also turns
+//     each chunk of rows into the policy observation rows (kernels_policy.cuh) on the way out.
 #pragma once
 #include "device_math.cuh"
 #include "engine.h"
