@@ -289,11 +289,12 @@ __device__ __forceinline__ bool lidar_consider(const LidarCtx &c, float relx, fl
 __device__ __forceinline__ int plane_mask(float pz, float bz, float d2, float zmin_obj, float zmax_obj)
 {
     int m = 0;
-    const float offs[3] = {kLidarCarOffset, kLidarRoadEdgeOffset, kLidarRoadLineOffset};
     const float inv = rcp_fast(d2);
-#pragma unroll
+    // (not unrolled, like the lane-stride loops of this kernel: k_obs is sensitive to its instruction footprint -
+    // unrolling these few loops cost 3.7 % of the launch in instruction-fetch stalls)
+#pragma unroll 1
     for (int p = 0; p < 3; p++) {
-        const float oz = __fadd_rn(pz, offs[p]);
+        const float oz = __fadd_rn(pz, p == 0 ? kLidarCarOffset : (p == 1 ? kLidarRoadEdgeOffset : kLidarRoadLineOffset));
         // The reference tests lz = (oz - bz) / d2 against the slab [zmin, zmax] (touching counts as inside). Float
         // subtraction never flips a sign, so that is zmin <= lz <= zmax, and an approximate quotient decides it
         // unless lz is within 1e-5 of a face: only then is the IEEE division evaluated (and never with a zero
@@ -410,6 +411,7 @@ __device__ __forceinline__ void flush_aligned(const float *stage, float *dst, in
     const int nq = (n - head) >> 2;
     const float4 *s4 = reinterpret_cast<const float4 *>(stage + mis + head);
     float4 *d4 = reinterpret_cast<float4 *>(dst + head);
+#pragma unroll 1
     for (int i = lane; i < nq; i += 32) d4[i] = s4[i];
     const int t0 = head + 4 * nq;
     if (lane < n - t0) dst[t0 + lane] = stage[mis + t0 + lane];

@@ -153,12 +153,14 @@ k_obs(const SceneDev *__restrict__ scenes, StateDev st, Exports ex, Params prm, 
     unsigned long long open[3] = {RAY_ALL, RAY_ALL, RAY_ALL};
     if (lidar_on) {
         __syncwarp();
+#pragma unroll 1
         for (int i = lane; i < 3 * NRAY; i += 32) wp.u.l.bt[i] = 0xffffffffu;
         const int controlled = ex.controlled[wa];
         const float head = controlled ? ex.action[wa * kActionSize + 2] : 0.f;   // sim.cpp:409
         float rgx, rgy, fwx, fwy;
         rotate_xy(qw, qz, 1.f, 0.f, rgx, rgy);     // rot.rotateVec(math::right)
         rotate_xy(qw, qz, 0.f, 1.f, fwx, fwy);     // rot.rotateVec(math::fwd)
+#pragma unroll 1
         for (int i = lane; i < NRAY; i += 32) {
             // (ray 0: 0 / NRAY = 0 without the slow path IEEE division takes for a zero operand)
             const float frac = i == 0 ? 0.f : __fdiv_rn(i == 0 ? 1.f : 2.f * (float)i, (float)NRAY);
@@ -340,6 +342,7 @@ k_obs(const SceneDev *__restrict__ scenes, StateDev st, Exports ex, Params prm, 
     if (lidar_on) {
         __syncwarp();
         float4 *out = reinterpret_cast<float4 *>(ex.lidar + wa * 3 * NRAY * kLidarRowSize);
+#pragma unroll 1
         for (int i = lane; i < 3 * NRAY; i += 32) {
             const uint32_t tbits = wp.u.l.bt[i];
             float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -465,6 +468,7 @@ k_obs(const SceneDev *__restrict__ scenes, StateDev st, Exports ex, Params prm, 
             }
         };
         __syncwarp();
+#pragma unroll 1
         for (int i = lane; i < 256; i += 32) wp.v.hist[i] = 0;
         __syncwarp();
         sweep_near([&](int, unsigned kb, bool in) { if (in) atomicAdd(&wp.v.hist[quant(kb)], 1u); });
@@ -494,8 +498,10 @@ k_obs(const SceneDev *__restrict__ scenes, StateDev st, Exports ex, Params prm, 
         // Fast path: one histogram pass over a monotone 8-bit quantisation of the key finds the bin that
         // holds the K-th smallest; its (few) members are then ranked exactly by (key, road index).
         __syncwarp();
+#pragma unroll 1
         for (int i = lane; i < 256; i += 32) wp.v.hist[i] = 0;
         __syncwarp();
+#pragma unroll 1
         for (int i = lane; i < C; i += 32) atomicAdd(&wp.v.hist[quant(wp.ckey[i])], 1u);
         __syncwarp();
         int digit, before, inbin;
@@ -535,9 +541,11 @@ k_obs(const SceneDev *__restrict__ scenes, StateDev st, Exports ex, Params prm, 
         for (int pass = 0; pass < 4; pass++) {
             const int shift = 24 - 8 * pass;
             __syncwarp();
+#pragma unroll 1
             for (int i = lane; i < 256; i += 32) wp.v.hist[i] = 0;
             __syncwarp();
             const unsigned hi_mask = pass == 0 ? 0u : (0xffffffffu << (shift + 8));
+#pragma unroll 1
             for (int i = lane; i < N; i += 32) {
                 unsigned kb; bool in = true;
                 if (overflow) in = slot_key(i, kb); else kb = wp.ckey[i];
@@ -582,6 +590,7 @@ k_obs(const SceneDev *__restrict__ scenes, StateDev st, Exports ex, Params prm, 
             unsigned last = 0; bool first = true;
             for (int r = 0; r < remaining; r++) {
                 unsigned best_idx = 0xffffffffu;
+#pragma unroll 1
                 for (int i = lane; i < N; i += 32) {
                     unsigned kb; bool in = true; int e = i;
                     if (overflow) in = slot_key(i, kb); else { kb = wp.ckey[i]; e = wp.cpos[i]; }
@@ -643,6 +652,7 @@ k_obs(const SceneDev *__restrict__ scenes, StateDev st, Exports ex, Params prm, 
         uint32_t *bm = reinterpret_cast<uint32_t *>(&wp.v);
         uint16_t *pre = wp.cpos;                                    // (the candidates are dead once the bit map is built)
         __syncwarp();
+#pragma unroll 1
         for (int i = lane; i < BMW; i += 32) bm[i] = 0u;
         __syncwarp();
         for (int base = 0; base < N; base += 32) {
@@ -722,11 +732,13 @@ k_obs(const SceneDev *__restrict__ scenes, StateDev st, Exports ex, Params prm, 
         float4 *d4 = reinterpret_cast<float4 *>(dst + head);
         const int nq = (n - head) >> 2;              // (K * 9 is a multiple of 4: no tail)
         if (first_k_only) {
+#pragma unroll 1
             for (int i = lane; i < nq; i += 32) {
                 const int j = head + 4 * i;
                 d4[i] = make_float4(padval(j), padval(j + 1), padval(j + 2), padval(j + 3));
             }
         } else {
+#pragma unroll 1
             for (int i = lane; i < nq; i += 32) d4[i] = make_float4(0.f, 0.f, 0.f, 0.f);
         }
         if (POL) {
@@ -736,6 +748,7 @@ k_obs(const SceneDev *__restrict__ scenes, StateDev st, Exports ex, Params prm, 
             policy_road_row<true>(zrow, true, o);
             float *pd = pol_road0() + (size_t)emitted * kPolicyRoad;
             const int np = (K - emitted) * kPolicyRoad;
+#pragma unroll 1
             for (int i = lane; i < np; i += 32) {
                 const int k = i % kPolicyRoad;
                 pd[i] = k < 2 ? o[0] : (k == 6 ? o[6] : o[2]);      // (o[1] == o[0]; o[2..5] and o[7..12] are equal too)
@@ -743,6 +756,7 @@ k_obs(const SceneDev *__restrict__ scenes, StateDev st, Exports ex, Params prm, 
         }
     }
     if (write_knn_idx)
+#pragma unroll 1
         for (int i = emitted + lane; i < K; i += 32) kidx[i] = -1;
 #ifndef GD_OBS_NO_COSTSORT
     if (lane == 0) st.cost[wa] = (unsigned)clock() - clk0;
