@@ -303,7 +303,9 @@ __device__ __forceinline__ int plane_mask(float pz, float bz, float d2, float zm
         const float q = num * inv;
         bool in = q >= zmin_obj && q <= zmax_obj;
         const float tol = 1e-5f * fmaxf(1.f, fabsf(q));
-        if (fabsf(q - zmin_obj) <= tol || fabsf(q - zmax_obj) <= tol) {
+        // (|q| >= 1e30: an agent parked at the padding position, z = FLT_MAX - far outside, and the IEEE division would
+        // overflow, which sends every warp that sees one such partner down the division's slow path)
+        if (fabsf(q) < 1e30f && (fabsf(q - zmin_obj) <= tol || fabsf(q - zmax_obj) <= tol)) {
             const float lz = num == 0.f ? 0.f : __fdiv_rn(num, d2);
             in = !(__fsub_rn(zmax_obj, lz) < 0.f) && !(__fsub_rn(lz, zmin_obj) < 0.f);
         }

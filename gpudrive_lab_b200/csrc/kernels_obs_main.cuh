@@ -231,7 +231,8 @@ k_obs(const SceneDev *__restrict__ scenes, StateDev st, Exports ex, Params prm, 
             // long thin runs of a polyline); the circle serves the angular tests below
             const float gex = fmaxf(fabsf(fmaf(relx, gb.x, rely * gb.y)) - gb.z, 0.f);
             const float gey = fmaxf(fabsf(fmaf(rely, gb.x, -(relx * gb.y))) - gb.w, 0.f);
-            const float dmin = fmaxf(sqrtf(fmaf(gex, gex, gey * gey)), fmaxf(d - gc.z, 0.f));
+            // (inside the rectangle gex = gey = 0, and sqrtf(0) takes its slow path: 1e-10 m decides nothing below)
+            const float dmin = fmaxf(sqrtf(fmaxf(fmaf(gex, gex, gey * gey), 1e-20f)), fmaxf(d - gc.z, 0.f));
             const bool nearg = valid && want_cands && dmin <= rpad;
             const unsigned cm = __float_as_uint(gc.w) & 0xffu;       // one z-class per group (classes are padded to 32)
             int pmg = (lidar_on && valid && cm && dmin <= kLidarDistance) ? (zmask_classes >> (3 * (__ffs(cm) - 1))) & 7 : 0;
