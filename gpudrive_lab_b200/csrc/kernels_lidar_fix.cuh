@@ -1,6 +1,6 @@
 // k_lidar_fix: exact re-trace of the few lidar rays k_obs does not settle.
 // k_obs finds candidate hits with fast arithmetic widened by a rounding bound; a hit inside that bound ("marginal":
-// grazed corner, origin on a face, range limit) that wins its ray - about one ray in 2 500 - is listed in
+// grazed corner, origin on a face, range limit) that wins its ray - about one ray in 28 000 - is listed in
 // StateDev::retrace instead of being exported. Here one warp takes one listed ray and clips it, with the reference's
 // exact arithmetic (broadphase.cpp:754-855), against every hull visible in its plane (the other agents, then the
 // road entities of every group whose bounding circle the ray can reach), one box per lane - first with the fast clip

@@ -365,7 +365,7 @@ k_obs(const SceneDev *__restrict__ scenes, StateDev st, Exports ex, Params prm, 
                 // A marginal winner (grazed corner, origin on a face, range limit) is not decided here: the ray goes to
                 // k_lidar_fix, which re-traces it with the reference's exact clip over every box. (Doing the exact clip
                 // here, and the re-trace as a call, cost every agent up to 25 % more time - 9.2 vs 7.7 ms per launch -
-                // for a path that about one ray in 2 500 takes.)
+                // for a path that about one ray in 28 000 takes.)
                 retrace = (id & 0x8000u) != 0;
                 const float2 d = wp.v.g.raydir[i % NRAY];
                 t = ray_box_exact_depth(px, py, bx, by, bqw, bqz, d0, d1, d.x, d.y);
